@@ -1,0 +1,548 @@
+// extern "C" layer of libb2conv.so -- see include/b2conv.h for the contract and the reference
+// interface each entry point replaces.  Host C++ only drives CUDA here; there is no CPU compute path.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/b2conv.h"
+#include "conv_params.h"
+#include "planner.h"
+
+namespace b2c {
+// conv_generic.cu
+cudaError_t launch_kspec(const ConvParams& p, int threads, size_t smem, cudaStream_t st);
+cudaError_t launch_conv_shared(const ConvParams& p, int grid, int threads, size_t smem, cudaStream_t st);
+cudaError_t launch_conv_perimage(const ConvParams& p, int grid, int threads, size_t smem, cudaStream_t st);
+int occupancy_conv_shared(int threads, size_t smem, bool in_smem);
+int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
+// conv_direct.cu
+size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out);
+cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
+int occupancy_direct(size_t smem);
+// util_kernels.cu
+cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long first, cudaStream_t st);
+cudaError_t launch_checksum(const double* d, long n, unsigned long long* d_out3, cudaStream_t st);
+}  // namespace b2c
+
+using namespace b2c;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                        \
+  do {                                                                                        \
+    cudaError_t e__ = (expr);                                                                 \
+    if (e__ != cudaSuccess)                                                                   \
+      return fail(e__ == cudaErrorMemoryAllocation ? B2C_ENOMEM : B2C_ECUDA, "%s failed: %s", \
+                  #expr, cudaGetErrorString(e__));                                            \
+  } while (0)
+
+struct AxisTables {
+  cplx* tw = nullptr;
+  int* neg = nullptr;
+};
+
+// Per-device cache: twiddle / partner tables keyed by period (cheap plan creation: the
+// reference's test driver calls init_workspace once per convolution, convolution_test.cc:109).
+struct DeviceCtx {
+  int dev = -1;
+  int sms = 0;
+  int smem_optin = 0;
+  std::map<int, AxisTables> tables;
+  unsigned long long* d_sum3 = nullptr;
+};
+
+std::mutex g_mu;
+std::map<int, DeviceCtx*> g_ctx;
+
+int get_ctx(DeviceCtx** out) {
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_ctx.find(dev);
+  if (it != g_ctx.end()) { *out = it->second; return 0; }
+  DeviceCtx* c = new DeviceCtx();
+  c->dev = dev;
+  CUDA_TRY(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, dev));
+  CUDA_TRY(cudaDeviceGetAttribute(&c->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  g_ctx[dev] = c;
+  *out = c;
+  return 0;
+}
+
+int get_tables(DeviceCtx* c, const AxisPlan& a, AxisTables* out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = c->tables.find(a.P);
+  if (it != c->tables.end()) { *out = it->second; return 0; }
+  const int P = a.P;
+  std::vector<cplx> tw(P);
+  const long double two_pi = 6.283185307179586476925286766559005768L;
+  for (int k = 0; k < P; ++k) {
+    // exact octant reduction keeps every twiddle correctly rounded
+    long double ang = two_pi * (long double)k / (long double)P;
+    tw[k] = make_double2((double)cosl(ang), (double)(-sinl(ang)));
+  }
+  std::vector<int> freq(P), pos_of(P), neg(P);
+  dif_permutation(P, a.nstages, a.radix, freq.data());
+  for (int p = 0; p < P; ++p) pos_of[freq[p]] = p;
+  for (int p = 0; p < P; ++p) neg[p] = pos_of[(P - freq[p]) % P];
+  AxisTables t;
+  CUDA_TRY(cudaMalloc(&t.tw, sizeof(cplx) * P));
+  CUDA_TRY(cudaMalloc(&t.neg, sizeof(int) * P));
+  CUDA_TRY(cudaMemcpy(t.tw, tw.data(), sizeof(cplx) * P, cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(t.neg, neg.data(), sizeof(int) * P, cudaMemcpyHostToDevice));
+  c->tables[P] = t;
+  *out = t;
+  return 0;
+}
+
+struct KernelTimer {
+  bool on = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
+  void clear() {
+    for (auto& e : ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    ev.clear();
+  }
+};
+KernelTimer g_timer;
+
+constexpr int kPipe = 3;
+
+}  // namespace
+
+struct b2c_plan {
+  Plan2D pl;
+  int forced_path = B2C_PATH_AUTO;
+  // lazily created device state (one device per plan)
+  DeviceCtx* ctx = nullptr;
+  AxisTables th, tw;
+  cplx* kspec = nullptr;
+  cplx* work = nullptr;
+  size_t work_slabs = 0;
+  // single-image host path staging
+  double* d_one = nullptr;
+  size_t d_one_bytes = 0;
+  // batched host pipeline
+  double* d_src[kPipe] = {nullptr, nullptr, nullptr};
+  double* d_ker[kPipe] = {nullptr, nullptr, nullptr};
+  double* d_dst[kPipe] = {nullptr, nullptr, nullptr};
+  long pipe_chunk = 0;
+  int pipe_shared = -1;
+  cudaStream_t s_h2d = nullptr, s_cmp = nullptr, s_d2h = nullptr;
+  cudaEvent_t ev_h2d[kPipe], ev_cmp[kPipe], ev_d2h[kPipe];
+  bool pipe_ready = false;
+};
+
+namespace {
+
+size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (size_t)pl.w.P; }
+
+// Cost-model crossover between the direct kernel and the FFT chain (refined by measurement,
+// see DESIGN.md): FP64 instruction estimates per image for both.
+int auto_path(const Plan2D& pl, bool shared) {
+  const double wkp = (pl.w.n_ker + 7) / 8 * 8, wdp = (pl.w.n_dst + 7) / 8 * 8;
+  const double direct = (double)pl.h.n_dst * wdp * pl.h.n_ker * wkp * 1.15;
+  const double rows = (double)pl.h.n_src + pl.h.lin;
+  double fft = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
+  if (shared) fft *= 0.5;  // two images per transform
+  fft *= 1.6;              // generic-path overhead (index arithmetic, barriers), measured factor
+  // the direct kernel must also fit its tile in shared memory
+  int spw;
+  if (direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, 8, &spw) > 200 * 1024) return B2C_PATH_FFT;
+  return direct <= fft ? B2C_PATH_DIRECT : B2C_PATH_FFT;
+}
+
+int ensure_device_state(b2c_plan* p) {
+  if (p->ctx) return 0;
+  DeviceCtx* c = nullptr;
+  if (int rc = get_ctx(&c)) return rc;
+  if (int rc = get_tables(c, p->pl.h, &p->th)) return rc;
+  if (int rc = get_tables(c, p->pl.w, &p->tw)) return rc;
+  p->ctx = c;
+  return 0;
+}
+
+void fill_axis(AxisDev& d, const AxisPlan& a, const AxisTables& t) {
+  d.P = a.P;
+  d.nstages = a.nstages;
+  for (int i = 0; i < 16; ++i) d.radix[i] = i < a.nstages ? a.radix[i] : 0;
+  d.tw = t.tw;
+  d.neg = t.neg;
+}
+
+int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst,
+                 long n, cudaStream_t st) {
+  if (int rc = ensure_device_state(p)) return rc;
+  const Plan2D& pl = p->pl;
+  ConvParams q;
+  memset(&q, 0, sizeof q);
+  q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
+  q.hd = pl.h.n_dst; q.wd = pl.w.n_dst;
+  q.off_h = pl.h.off; q.off_w = pl.w.off; q.fold_h = pl.h.fold; q.fold_w = pl.w.fold;
+  q.lin_h = pl.h.lin; q.lin_w = pl.w.lin; q.kwrap_h = pl.h.kwrap; q.kwrap_w = pl.w.kwrap;
+  q.ld = pl.w.P;
+  fill_axis(q.ah, pl.h, p->th);
+  fill_axis(q.aw, pl.w, p->tw);
+  q.scale = 1.0 / ((double)pl.h.P * (double)pl.w.P);
+  q.src = d_src; q.ker = d_ker; q.dst = d_dst; q.n_images = n;
+  const size_t wb = work_bytes(pl);
+  q.work_in_smem = wb <= (size_t)p->ctx->smem_optin ? 1 : 0;
+  const int threads = (size_t)pl.h.P * pl.w.P >= 6144 ? 512 : 256;
+  const long units = shared ? (n + 1) / 2 : n;
+  int occ = shared ? occupancy_conv_shared(threads, wb, q.work_in_smem)
+                   : occupancy_conv_perimage(threads, wb, q.work_in_smem);
+  if (occ < 1) return fail(B2C_ECUDA, "convolution kernel cannot be resident (threads=%d smem=%zu)", threads, wb);
+  int grid = (int)std::min<long>(units, (long)p->ctx->sms * occ);
+  if (grid < 1) grid = 1;
+  if (!q.work_in_smem) {
+    const size_t slabs = (size_t)std::max(grid, 1);
+    if (p->work_slabs < slabs) {
+      if (p->work) cudaFree(p->work);
+      p->work = nullptr; p->work_slabs = 0;
+      CUDA_TRY(cudaMalloc(&p->work, wb * (size_t)p->ctx->sms * occ));
+      p->work_slabs = (size_t)p->ctx->sms * occ;
+    }
+    q.work = p->work;
+  }
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (shared) {
+    if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, wb));
+    q.kspec = p->kspec;
+    CUDA_TRY(launch_kspec(q, 512, wb, st));
+    ++g_launches;
+  }
+  if (g_timer.on && g_timer.ev.size() < 8192) {
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, st));
+  }
+  if (shared) CUDA_TRY(launch_conv_shared(q, grid, threads, wb, st));
+  else CUDA_TRY(launch_conv_perimage(q, grid, threads, wb, st));
+  ++g_launches;
+  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  return 0;
+}
+
+int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst,
+                    long n, cudaStream_t st) {
+  if (int rc = ensure_device_state(p)) return rc;
+  const Plan2D& pl = p->pl;
+  DirectParams q;
+  memset(&q, 0, sizeof q);
+  q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
+  q.hd = pl.h.n_dst; q.wd = pl.w.n_dst; q.off_h = pl.h.off; q.off_w = pl.w.off;
+  q.wrap_h = pl.mode == B2C_CIRCULAR_SAME ? pl.h.n_src : 0;
+  q.wrap_w = pl.mode == B2C_CIRCULAR_SAME ? pl.w.n_src : 0;
+  q.kernel_is_shared = shared;
+  q.src = d_src; q.ker = d_ker; q.dst = d_dst; q.n_images = n;
+  // largest row tile that leaves room for two CTAs per SM, else the largest that fits at all
+  const size_t budget2 = (size_t)p->ctx->smem_optin / 2 - 1024, budget1 = (size_t)p->ctx->smem_optin;
+  int tile = q.hd, spw = 0;
+  while (tile > 1 && direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw) > budget2) tile = (tile + 1) / 2;
+  if (direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw) > budget1)
+    return fail(B2C_ESIZE, "direct kernel: %dx%d kernel does not fit in shared memory", q.hk, q.wk);
+  q.tile_h = tile;
+  q.tiles_per_image = (q.hd + tile - 1) / tile;
+  const size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw);
+  q.sp_w = spw;
+  int occ = occupancy_direct(smem);
+  if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
+  const long total = n * q.tiles_per_image;
+  int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);
+  if (grid < 1) grid = 1;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_timer.on && g_timer.ev.size() < 8192) {
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, st));
+  }
+  CUDA_TRY(launch_direct(q, grid, smem, st));
+  ++g_launches;
+  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  return 0;
+}
+
+int effective_path(const b2c_plan* p, int shared) {
+  if (p->forced_path != B2C_PATH_AUTO) return p->forced_path;
+  return auto_path(p->pl, shared != 0);
+}
+
+void free_pipe(b2c_plan* p) {
+  for (int i = 0; i < kPipe; ++i) {
+    if (p->d_src[i]) cudaFree(p->d_src[i]);
+    if (p->d_ker[i]) cudaFree(p->d_ker[i]);
+    if (p->d_dst[i]) cudaFree(p->d_dst[i]);
+    p->d_src[i] = p->d_ker[i] = p->d_dst[i] = nullptr;
+  }
+  p->pipe_chunk = 0;
+  p->pipe_shared = -1;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b2c_last_error(void) { return g_err.c_str(); }
+const char* b2c_version(void) { return "b2conv 0.1 (sm_100a)"; }
+long b2c_launch_count(void) { return g_launches.load(); }
+
+int b2c_set_device(int device) {
+  CUDA_TRY(cudaSetDevice(device));
+  return 0;
+}
+
+int b2c_find_closest_factor(int n) { return ref_find_closest_factor(n); }
+int b2c_smooth_size(int n) { return choose_period(n); }
+
+int b2c_partition(long n, int world, int rank, long* begin, long* end) {
+  if (n < 0 || world < 1 || rank < 0 || rank >= world || !begin || !end)
+    return fail(B2C_EINVAL, "b2c_partition: bad arguments n=%ld world=%d rank=%d", n, world, rank);
+  const long per = (n + world - 1) / world;  // GPU g owns [g*ceil(N/G), min(N,(g+1)*ceil(N/G)))
+  *begin = std::min(n, per * rank);
+  *end = std::min(n, per * (rank + 1));
+  return 0;
+}
+
+int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kernel, int w_kernel) {
+  if (!plan) return fail(B2C_EINVAL, "b2c_plan_create: null out pointer");
+  *plan = nullptr;
+  if (mode < 0 || mode > 7)
+    return fail(B2C_EINVAL,
+                "Unrecognized convolution mode %d, possible modes are: LINEAR_FULL(0) LINEAR_SAME_UNPADDED(1) "
+                "LINEAR_SAME(2) LINEAR_VALID(3) CIRCULAR_SAME(4) CIRCULAR_SAME_PADDED(5) "
+                "CIRCULAR_FULL_UNPADDED(6) CIRCULAR_FULL(7)", mode);
+  if (h_src < 1 || w_src < 1 || h_kernel < 1 || w_kernel < 1)
+    return fail(B2C_EINVAL, "b2c_plan_create: sizes must be positive (got %dx%d, %dx%d)", h_src, w_src,
+                h_kernel, w_kernel);
+  if ((long)h_src * w_src > (1L << 26) || (long)h_kernel * w_kernel > (1L << 26))
+    return fail(B2C_ESIZE, "b2c_plan_create: image too large");
+  b2c_plan* p = new b2c_plan();
+  if (!make_plan(mode, h_src, w_src, h_kernel, w_kernel, p->pl)) {
+    delete p;
+    return fail(B2C_EINVAL, "b2c_plan_create: planning failed");
+  }
+  *plan = p;
+  return 0;
+}
+
+int b2c_plan_query(const b2c_plan* p, int* h_fft, int* w_fft, int* h_dst, int* w_dst) {
+  if (!p) return fail(B2C_EINVAL, "b2c_plan_query: null plan");
+  if (h_fft) *h_fft = p->pl.empty ? 0 : p->pl.h.P;
+  if (w_fft) *w_fft = p->pl.empty ? 0 : p->pl.w.P;
+  if (h_dst) *h_dst = p->pl.empty ? 0 : p->pl.h.n_dst;
+  if (w_dst) *w_dst = p->pl.empty ? 0 : p->pl.w.n_dst;
+  return 0;
+}
+
+int b2c_plan_info(const b2c_plan* p, int* path, int* off_h, int* off_w, int* fold_h, int* fold_w,
+                  long* wbytes, int* work_in_smem) {
+  if (!p) return fail(B2C_EINVAL, "b2c_plan_info: null plan");
+  if (path) *path = p->pl.empty ? B2C_PATH_AUTO : effective_path(p, 1);
+  if (off_h) *off_h = p->pl.h.off;
+  if (off_w) *off_w = p->pl.w.off;
+  if (fold_h) *fold_h = p->pl.h.fold;
+  if (fold_w) *fold_w = p->pl.w.fold;
+  if (wbytes) *wbytes = p->pl.empty ? 0 : (long)work_bytes(p->pl);
+  if (work_in_smem) *work_in_smem = p->pl.empty ? 0 : (work_bytes(p->pl) <= 232448 ? 1 : 0);
+  return 0;
+}
+
+int b2c_plan_set_path(b2c_plan* p, int path) {
+  if (!p || path < 0 || path > 2) return fail(B2C_EINVAL, "b2c_plan_set_path: bad arguments");
+  p->forced_path = path;
+  return 0;
+}
+
+int b2c_plan_destroy(b2c_plan* p) {
+  if (!p) return 0;
+  if (p->kspec) cudaFree(p->kspec);
+  if (p->work) cudaFree(p->work);
+  if (p->d_one) cudaFree(p->d_one);
+  free_pipe(p);
+  if (p->pipe_ready) {
+    for (int i = 0; i < kPipe; ++i) {
+      cudaEventDestroy(p->ev_h2d[i]); cudaEventDestroy(p->ev_cmp[i]); cudaEventDestroy(p->ev_d2h[i]);
+    }
+    cudaStreamDestroy(p->s_h2d); cudaStreamDestroy(p->s_cmp); cudaStreamDestroy(p->s_d2h);
+  }
+  delete p;
+  return 0;
+}
+
+int b2c_convolve_batch_device(b2c_plan* p, const double* d_src, const double* d_kernel,
+                              int kernel_is_shared, double* d_dst, long n_images, void* cuda_stream) {
+  if (!p) return fail(B2C_EINVAL, "b2c_convolve_batch_device: null plan");
+  if (n_images < 0) return fail(B2C_EINVAL, "b2c_convolve_batch_device: negative batch");
+  if (p->pl.empty || n_images == 0) return 0;  // convolution_fftw.h:218-219
+  if (!d_src || !d_kernel || !d_dst) return fail(B2C_EINVAL, "b2c_convolve_batch_device: null buffer");
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  if (effective_path(p, kernel_is_shared) == B2C_PATH_DIRECT)
+    return run_direct_path(p, d_src, d_kernel, kernel_is_shared, d_dst, n_images, st);
+  return run_fft_path(p, d_src, d_kernel, kernel_is_shared, d_dst, n_images, st);
+}
+
+int b2c_convolve_host(b2c_plan* p, const double* src, const double* kernel, double* dst) {
+  if (!p) return fail(B2C_EINVAL, "b2c_convolve_host: null plan");
+  if (p->pl.empty) return 0;
+  if (!src || !kernel || !dst) return fail(B2C_EINVAL, "b2c_convolve_host: null buffer");
+  const Plan2D& pl = p->pl;
+  const size_t sb = sizeof(double) * pl.h.n_src * pl.w.n_src;
+  const size_t kb = sizeof(double) * pl.h.n_ker * pl.w.n_ker;
+  const size_t db = sizeof(double) * pl.h.n_dst * pl.w.n_dst;
+  auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+  const size_t need = up(sb) + up(kb) + up(db);
+  if (p->d_one_bytes < need) {
+    if (p->d_one) cudaFree(p->d_one);
+    p->d_one = nullptr; p->d_one_bytes = 0;
+    CUDA_TRY(cudaMalloc(&p->d_one, need));
+    p->d_one_bytes = need;
+  }
+  char* base = reinterpret_cast<char*>(p->d_one);
+  double* ds = reinterpret_cast<double*>(base);
+  double* dk = reinterpret_cast<double*>(base + up(sb));
+  double* dd = reinterpret_cast<double*>(base + up(sb) + up(kb));
+  CUDA_TRY(cudaMemcpyAsync(ds, src, sb, cudaMemcpyHostToDevice, 0));
+  CUDA_TRY(cudaMemcpyAsync(dk, kernel, kb, cudaMemcpyHostToDevice, 0));
+  if (int rc = b2c_convolve_batch_device(p, ds, dk, 1, dd, 1, nullptr)) return rc;
+  CUDA_TRY(cudaMemcpyAsync(dst, dd, db, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return 0;
+}
+
+int b2c_convolve_batch_host(b2c_plan* p, const double* src, const double* kernel, int kernel_is_shared,
+                            double* dst, long n_images) {
+  if (!p) return fail(B2C_EINVAL, "b2c_convolve_batch_host: null plan");
+  if (n_images < 0) return fail(B2C_EINVAL, "b2c_convolve_batch_host: negative batch");
+  if (p->pl.empty || n_images == 0) return 0;
+  if (!src || !kernel || !dst) return fail(B2C_EINVAL, "b2c_convolve_batch_host: null buffer");
+  const Plan2D& pl = p->pl;
+  const size_t sn = (size_t)pl.h.n_src * pl.w.n_src, kn = (size_t)pl.h.n_ker * pl.w.n_ker;
+  const size_t dn = (size_t)pl.h.n_dst * pl.w.n_dst;
+  if (!p->pipe_ready) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&p->s_h2d, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&p->s_cmp, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&p->s_d2h, cudaStreamNonBlocking));
+    for (int i = 0; i < kPipe; ++i) {
+      CUDA_TRY(cudaEventCreateWithFlags(&p->ev_h2d[i], cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&p->ev_cmp[i], cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&p->ev_d2h[i], cudaEventDisableTiming));
+    }
+    p->pipe_ready = true;
+  }
+  // chunk: ~48 MB of traffic per stage keeps the three engines busy without hoarding HBM
+  const size_t per_img = sizeof(double) * (sn + dn + (kernel_is_shared ? 0 : kn));
+  long chunk = (long)std::max<size_t>(2, (48u << 20) / std::max<size_t>(per_img, 1));
+  chunk = std::min(chunk, n_images);
+  if (chunk & 1) ++chunk;  // keep image pairs together
+  if (p->pipe_chunk < chunk || p->pipe_shared != kernel_is_shared) {
+    free_pipe(p);
+    for (int i = 0; i < kPipe; ++i) {
+      CUDA_TRY(cudaMalloc(&p->d_src[i], sizeof(double) * sn * chunk));
+      CUDA_TRY(cudaMalloc(&p->d_dst[i], sizeof(double) * dn * chunk));
+      CUDA_TRY(cudaMalloc(&p->d_ker[i], sizeof(double) * kn * (kernel_is_shared ? 1 : chunk)));
+    }
+    p->pipe_chunk = chunk;
+    p->pipe_shared = kernel_is_shared;
+  }
+  long done = 0;
+  for (long c = 0; done < n_images; ++c) {
+    const int b = (int)(c % kPipe);
+    const long m = std::min(chunk, n_images - done);
+    if (c >= kPipe) CUDA_TRY(cudaStreamWaitEvent(p->s_h2d, p->ev_d2h[b], 0));
+    CUDA_TRY(cudaMemcpyAsync(p->d_src[b], src + done * sn, sizeof(double) * sn * m, cudaMemcpyHostToDevice, p->s_h2d));
+    if (kernel_is_shared)
+      CUDA_TRY(cudaMemcpyAsync(p->d_ker[b], kernel, sizeof(double) * kn, cudaMemcpyHostToDevice, p->s_h2d));
+    else
+      CUDA_TRY(cudaMemcpyAsync(p->d_ker[b], kernel + done * kn, sizeof(double) * kn * m, cudaMemcpyHostToDevice, p->s_h2d));
+    CUDA_TRY(cudaEventRecord(p->ev_h2d[b], p->s_h2d));
+    CUDA_TRY(cudaStreamWaitEvent(p->s_cmp, p->ev_h2d[b], 0));
+    if (int rc = b2c_convolve_batch_device(p, p->d_src[b], p->d_ker[b], kernel_is_shared, p->d_dst[b], m, p->s_cmp))
+      return rc;
+    CUDA_TRY(cudaEventRecord(p->ev_cmp[b], p->s_cmp));
+    CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, p->ev_cmp[b], 0));
+    CUDA_TRY(cudaMemcpyAsync(dst + done * dn, p->d_dst[b], sizeof(double) * dn * m, cudaMemcpyDeviceToHost, p->s_d2h));
+    CUDA_TRY(cudaEventRecord(p->ev_d2h[b], p->s_d2h));
+    done += m;
+  }
+  CUDA_TRY(cudaStreamSynchronize(p->s_d2h));
+  CUDA_TRY(cudaStreamSynchronize(p->s_cmp));
+  CUDA_TRY(cudaStreamSynchronize(p->s_h2d));
+  return 0;
+}
+
+int b2c_checksum_device(const double* d, long n, unsigned long long* out3, void* cuda_stream) {
+  if (!out3 || n < 0 || (n > 0 && !d)) return fail(B2C_EINVAL, "b2c_checksum_device: bad arguments");
+  DeviceCtx* c = nullptr;
+  if (int rc = get_ctx(&c)) return rc;
+  if (!c->d_sum3) CUDA_TRY(cudaMalloc(&c->d_sum3, 3 * sizeof(unsigned long long)));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  CUDA_TRY(cudaMemsetAsync(c->d_sum3, 0, 3 * sizeof(unsigned long long), st));
+  if (n > 0) {
+    CUDA_TRY(launch_checksum(d, n, c->d_sum3, st));
+    ++g_launches;
+  }
+  CUDA_TRY(cudaMemcpyAsync(out3, c->d_sum3, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int b2c_fill_uniform_device(double* d, long n, unsigned long long seed, long first, void* cuda_stream) {
+  if (n < 0 || (n > 0 && !d)) return fail(B2C_EINVAL, "b2c_fill_uniform_device: bad arguments");
+  if (n == 0) return 0;
+  CUDA_TRY(launch_fill_uniform(d, n, seed, first, (cudaStream_t)cuda_stream));
+  ++g_launches;
+  return 0;
+}
+
+int b2c_host_alloc(void** p, long bytes) {
+  if (!p || bytes < 0) return fail(B2C_EINVAL, "b2c_host_alloc: bad arguments");
+  CUDA_TRY(cudaHostAlloc(p, (size_t)std::max<long>(bytes, 1), cudaHostAllocDefault));
+  return 0;
+}
+
+int b2c_host_free(void* p) {
+  if (p) CUDA_TRY(cudaFreeHost(p));
+  return 0;
+}
+
+int b2c_kernel_timer(int enable) {
+  g_timer.clear();
+  g_timer.on = enable != 0;
+  return 0;
+}
+
+int b2c_kernel_timer_read(double* avg_ms, long* launches) {
+  double total = 0;
+  long n = 0;
+  for (auto& e : g_timer.ev) {
+    CUDA_TRY(cudaEventSynchronize(e.second));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e.first, e.second));
+    total += ms;
+    ++n;
+  }
+  if (avg_ms) *avg_ms = n ? total / n : 0.0;
+  if (launches) *launches = n;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,42 @@
+// Kernel parameter block shared by host (capi.cu) and device (conv_generic.cu, conv_direct.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "fft_device.cuh"
+
+namespace b2c {
+
+struct ConvParams {
+  // geometry (reference names: h_src,w_src,h_kernel,w_kernel,h_dst,w_dst -- convolution_fftw.h:29-42)
+  int hs, ws, hk, wk, hd, wd;
+  int off_h, off_w;      // crop origin inside the linear result (convolution_fftw.h:227-272)
+  int fold_h, fold_w;    // >0: fold the linear result modulo this on store (CIRCULAR_SAME)
+  int lin_h, lin_w;      // extent of the linear result that has to be produced
+  int kwrap_h, kwrap_w;  // kernel taps wrap-accumulate modulo these (convolution_fftw.h:185-187)
+  int ld;                // leading dimension (complex elements) of the work buffer
+  AxisDev ah, aw;
+  double scale;          // 1 / (P_h * P_w)            (convolution_fftw.h:210-211)
+  const double* src;     // [n][hs][ws]
+  const double* ker;     // [hk][wk] or [n][hk][wk]
+  double* dst;           // [n][hd][wd]
+  long n_images;
+  cplx* kspec;           // shared-kernel spectrum, P_h x P_w, scrambled order, pre-scaled
+  cplx* work;            // global work slabs [gridDim.x][P_h*ld] when the image does not fit in smem
+  int work_in_smem;
+};
+
+struct DirectParams {
+  int hs, ws, hk, wk, hd, wd;
+  int off_h, off_w;
+  int wrap_h, wrap_w;    // >0: source indices wrap modulo this (CIRCULAR_SAME), else zero outside
+  int tile_h;            // output rows per CTA
+  int tiles_per_image;
+  int sp_w;              // padded staged-source row length (doubles)
+  int kernel_is_shared;
+  const double* src;
+  const double* ker;
+  double* dst;
+  long n_images;
+};
+
+}  // namespace b2c

@@ -1,0 +1,241 @@
+// Device-side FFT building blocks of the generic (any 2/3/5/7-smooth size) convolution path.
+//
+// Transform scheme: IN-PLACE decimation in frequency for the forward transform (natural order
+// in, digit-scrambled order out) and its exact mirror, decimation in time, for the backward
+// transform (scrambled in, natural out).  A convolution multiplies two spectra that were
+// scrambled by the same schedule, so no reordering pass is ever needed and one work buffer per
+// image is enough (no Stockham ping-pong copy) -- half the shared memory of an autosort FFT.
+//
+// Replaces the three fftw_execute calls of the reference (convolution_fftw.h:190-191,208).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace b2c {
+
+typedef double2 cplx;
+
+__device__ __forceinline__ cplx cadd(cplx a, cplx b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ cplx csub(cplx a, cplx b) { return make_double2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ cplx cmul(cplx a, cplx b) {
+  return make_double2(fma(a.x, b.x, -a.y * b.y), fma(a.x, b.y, a.y * b.x));
+}
+// a * conj(b)
+__device__ __forceinline__ cplx cmulc(cplx a, cplx b) {
+  return make_double2(fma(a.x, b.x, a.y * b.y), fma(a.y, b.x, -a.x * b.y));
+}
+// -i * a
+__device__ __forceinline__ cplx mul_mi(cplx a) { return make_double2(a.y, -a.x); }
+// +i * a
+__device__ __forceinline__ cplx mul_pi(cplx a) { return make_double2(-a.y, a.x); }
+__device__ __forceinline__ cplx cswap(cplx a) { return make_double2(a.y, a.x); }
+
+// ---- forward DFT butterflies, w = exp(-2*pi*i/R), in registers --------------------------------
+template <int R>
+struct Bfly;
+
+template <>
+struct Bfly<2> {
+  static __device__ __forceinline__ void run(cplx* v) {
+    cplx a = v[0], b = v[1];
+    v[0] = cadd(a, b);
+    v[1] = csub(a, b);
+  }
+};
+
+template <>
+struct Bfly<3> {
+  static __device__ __forceinline__ void run(cplx* v) {
+    const double s = 0.86602540378443864676;  // sin(2*pi/3)
+    cplx t = cadd(v[1], v[2]);
+    cplx d = csub(v[1], v[2]);
+    cplx m = make_double2(fma(-0.5, t.x, v[0].x), fma(-0.5, t.y, v[0].y));
+    v[0] = cadd(v[0], t);
+    // X1 = m - i*s*d ; X2 = m + i*s*d
+    v[1] = make_double2(fma(s, d.y, m.x), fma(-s, d.x, m.y));
+    v[2] = make_double2(fma(-s, d.y, m.x), fma(s, d.x, m.y));
+  }
+};
+
+template <>
+struct Bfly<4> {
+  static __device__ __forceinline__ void run(cplx* v) {
+    cplx a = cadd(v[0], v[2]), b = csub(v[0], v[2]);
+    cplx c = cadd(v[1], v[3]), d = mul_mi(csub(v[1], v[3]));
+    v[0] = cadd(a, c);
+    v[1] = cadd(b, d);
+    v[2] = csub(a, c);
+    v[3] = csub(b, d);
+  }
+};
+
+template <>
+struct Bfly<5> {
+  static __device__ __forceinline__ void run(cplx* v) {
+    const double c1 = 0.30901699437494742410;   // cos(2*pi/5)
+    const double c2 = -0.80901699437494742410;  // cos(4*pi/5)
+    const double s1 = 0.95105651629515357212;   // sin(2*pi/5)
+    const double s2 = 0.58778525229247312917;   // sin(4*pi/5)
+    cplx t1 = cadd(v[1], v[4]), t2 = cadd(v[2], v[3]);
+    cplx t3 = csub(v[1], v[4]), t4 = csub(v[2], v[3]);
+    cplx x0 = v[0];
+    cplx m1 = make_double2(fma(c2, t2.x, fma(c1, t1.x, x0.x)), fma(c2, t2.y, fma(c1, t1.y, x0.y)));
+    cplx m2 = make_double2(fma(c1, t2.x, fma(c2, t1.x, x0.x)), fma(c1, t2.y, fma(c2, t1.y, x0.y)));
+    cplx n1 = make_double2(fma(s2, t4.x, s1 * t3.x), fma(s2, t4.y, s1 * t3.y));
+    cplx n2 = make_double2(fma(-s1, t4.x, s2 * t3.x), fma(-s1, t4.y, s2 * t3.y));
+    v[0] = cadd(x0, cadd(t1, t2));
+    v[1] = make_double2(m1.x + n1.y, m1.y - n1.x);  // m1 - i n1
+    v[4] = make_double2(m1.x - n1.y, m1.y + n1.x);  // m1 + i n1
+    v[2] = make_double2(m2.x + n2.y, m2.y - n2.x);
+    v[3] = make_double2(m2.x - n2.y, m2.y + n2.x);
+  }
+};
+
+template <>
+struct Bfly<7> {
+  static __device__ __forceinline__ void run(cplx* v) {
+    const double c1 = 0.62348980185873353053;   // cos(2*pi/7)
+    const double c2 = -0.22252093395631440429;  // cos(4*pi/7)
+    const double c3 = -0.90096886790241912624;  // cos(6*pi/7)
+    const double s1 = 0.78183148246802980871;   // sin(2*pi/7)
+    const double s2 = 0.97492791218182360702;   // sin(4*pi/7)
+    const double s3 = 0.43388373911755812048;   // sin(6*pi/7)
+    cplx ta = cadd(v[1], v[6]), tb = cadd(v[2], v[5]), tc = cadd(v[3], v[4]);
+    cplx da = csub(v[1], v[6]), db = csub(v[2], v[5]), dc = csub(v[3], v[4]);
+    cplx x0 = v[0];
+    // symmetric parts: M_m = x0 + c(m)ta + c(2m)tb + c(3m)tc  (indices mod 7, cos even)
+    cplx M1 = make_double2(fma(c3, tc.x, fma(c2, tb.x, fma(c1, ta.x, x0.x))),
+                           fma(c3, tc.y, fma(c2, tb.y, fma(c1, ta.y, x0.y))));
+    cplx M2 = make_double2(fma(c1, tc.x, fma(c3, tb.x, fma(c2, ta.x, x0.x))),
+                           fma(c1, tc.y, fma(c3, tb.y, fma(c2, ta.y, x0.y))));
+    cplx M3 = make_double2(fma(c2, tc.x, fma(c1, tb.x, fma(c3, ta.x, x0.x))),
+                           fma(c2, tc.y, fma(c1, tb.y, fma(c3, ta.y, x0.y))));
+    // antisymmetric parts: N_m = s(m)da + s(2m)db + s(3m)dc  (sin odd: s(4)=-s3, s(6)=-s1, s(9)=s2)
+    cplx N1 = make_double2(fma(s3, dc.x, fma(s2, db.x, s1 * da.x)),
+                           fma(s3, dc.y, fma(s2, db.y, s1 * da.y)));
+    cplx N2 = make_double2(fma(-s1, dc.x, fma(-s3, db.x, s2 * da.x)),
+                           fma(-s1, dc.y, fma(-s3, db.y, s2 * da.y)));
+    cplx N3 = make_double2(fma(s2, dc.x, fma(-s1, db.x, s3 * da.x)),
+                           fma(s2, dc.y, fma(-s1, db.y, s3 * da.y)));
+    v[0] = cadd(cadd(x0, ta), cadd(tb, tc));
+    v[1] = make_double2(M1.x + N1.y, M1.y - N1.x);
+    v[6] = make_double2(M1.x - N1.y, M1.y + N1.x);
+    v[2] = make_double2(M2.x + N2.y, M2.y - N2.x);
+    v[5] = make_double2(M2.x - N2.y, M2.y + N2.x);
+    v[3] = make_double2(M3.x + N3.y, M3.y - N3.x);
+    v[4] = make_double2(M3.x - N3.y, M3.y + N3.x);
+  }
+};
+
+template <>
+struct Bfly<8> {
+  static __device__ __forceinline__ void run(cplx* v) {
+    const double h = 0.70710678118654752440;  // 1/sqrt(2)
+    cplx e[4] = {v[0], v[2], v[4], v[6]};
+    cplx o[4] = {v[1], v[3], v[5], v[7]};
+    Bfly<4>::run(e);
+    Bfly<4>::run(o);
+    // o[k] *= w8^k
+    cplx o1 = make_double2(h * (o[1].x + o[1].y), h * (o[1].y - o[1].x));   // (1-i)/sqrt2
+    cplx o2 = mul_mi(o[2]);
+    cplx o3 = make_double2(h * (o[3].y - o[3].x), -h * (o[3].x + o[3].y));  // (-1-i)/sqrt2
+    v[0] = cadd(e[0], o[0]); v[4] = csub(e[0], o[0]);
+    v[1] = cadd(e[1], o1);   v[5] = csub(e[1], o1);
+    v[2] = cadd(e[2], o2);   v[6] = csub(e[2], o2);
+    v[3] = cadd(e[3], o3);   v[7] = csub(e[3], o3);
+  }
+};
+
+// One radix-R stage over `nlines` independent lines living in one work buffer.
+//   element k of line l is at  W[l*ls + k*es]
+//   P    : transform length;  n : current block length (n % R == 0);  m = n / R
+//   tw   : tw[k] = exp(-2*pi*i*k/P), k in [0,P)
+// Forward (INV=false): DIF -- butterfly, then multiply output q by w_n^(j*q).
+// Backward (INV=true) : DIT mirror -- multiply input q by conj(w_n^(j*q)), then inverse butterfly.
+// The inverse butterfly is the forward one with re/im swapped on the way in and out.
+// `line_fastest` chooses which task index varies fastest across threads so that the unit-stride
+// dimension is the one adjacent threads walk (rows: the element index; columns: the line index).
+template <int R, bool INV>
+__device__ __forceinline__ void fft_stage(cplx* W, int es, int ls, int nlines, int P, int n,
+                                          const cplx* __restrict__ tw, bool line_fastest) {
+  const int m = n / R;
+  const int per_line = P / R;
+  const int total = nlines * per_line;
+  const int tstep = P / n;
+  for (int task = threadIdx.x; task < total; task += blockDim.x) {
+    int line, t;
+    if (line_fastest) { t = task / nlines; line = task - t * nlines; }
+    else { line = task / per_line; t = task - line * per_line; }
+    const int b = t / m;
+    const int j = t - b * m;
+    cplx* p = W + (size_t)line * ls + (size_t)(b * n + j) * es;
+    const int stride = m * es;
+    cplx v[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) v[q] = p[q * stride];
+    if (INV) {
+      if (j != 0) {
+#pragma unroll
+        for (int q = 1; q < R; ++q) v[q] = cmulc(v[q], __ldg(&tw[j * q * tstep]));
+      }
+#pragma unroll
+      for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
+      Bfly<R>::run(v);
+#pragma unroll
+      for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
+    } else {
+      Bfly<R>::run(v);
+      if (j != 0) {
+#pragma unroll
+        for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(&tw[j * q * tstep]));
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q) p[q * stride] = v[q];
+  }
+}
+
+template <bool INV>
+__device__ __forceinline__ void fft_stage_dispatch(int R, cplx* W, int es, int ls, int nlines, int P,
+                                                   int n, const cplx* __restrict__ tw, bool lf) {
+  switch (R) {
+    case 2: fft_stage<2, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 3: fft_stage<3, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 4: fft_stage<4, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 5: fft_stage<5, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 7: fft_stage<7, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 8: fft_stage<8, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+  }
+}
+
+struct AxisDev {
+  int P;
+  int nstages;
+  int radix[16];
+  const cplx* tw;   // exp(-2*pi*i*k/P)
+  const int* neg;   // neg[pos] = position holding frequency (-freq(pos)) mod P   (scrambled order)
+};
+
+// Forward transform of `nlines` lines (starting at W, i.e. the caller offsets W to the first line).
+// Ends with a __syncthreads().
+__device__ __forceinline__ void fft_forward(const AxisDev& ax, cplx* W, int es, int ls, int nlines, bool lf) {
+  int n = ax.P;
+  for (int s = 0; s < ax.nstages; ++s) {
+    const int R = ax.radix[s];
+    fft_stage_dispatch<false>(R, W, es, ls, nlines, ax.P, n, ax.tw, lf);
+    n /= R;
+    __syncthreads();
+  }
+}
+
+// Backward (unnormalised) transform: the forward stages undone in reverse order.
+__device__ __forceinline__ void fft_backward(const AxisDev& ax, cplx* W, int es, int ls, int nlines, bool lf) {
+  int n = 1;
+  for (int s = ax.nstages - 1; s >= 0; --s) {
+    const int R = ax.radix[s];
+    n *= R;
+    fft_stage_dispatch<true>(R, W, es, ls, nlines, ax.P, n, ax.tw, lf);
+    __syncthreads();
+  }
+}
+
+}  // namespace b2c

@@ -1,0 +1,202 @@
+// Host-side planner.  See planner.h.  Pure C++ (no CUDA) so that planning works on a CPU-only box.
+#include "planner.h"
+
+#include <algorithm>
+#include <vector>
+
+namespace b2c {
+
+bool is_smooth2357(int n) {
+  if (n < 1) return false;
+  for (int p : {2, 3, 5, 7})
+    while (n % p == 0) n /= p;
+  return n == 1;
+}
+
+int next_smooth2357(int n) {
+  if (n < 1) n = 1;
+  while (!is_smooth2357(n)) ++n;
+  return n;
+}
+
+int radix_schedule(int n, int* radix) {
+  int e2 = 0, ns = 0;
+  int rem = n;
+  while (rem % 2 == 0) { rem /= 2; ++e2; }
+  // ascending radices: the last (largest) stage is the one that needs no twiddles
+  if (e2 % 3 == 1) { radix[ns++] = 2; e2 -= 1; }
+  while (rem % 3 == 0) { radix[ns++] = 3; rem /= 3; }
+  if (e2 % 3 == 2) { radix[ns++] = 4; e2 -= 2; }
+  while (rem % 5 == 0) { radix[ns++] = 5; rem /= 5; }
+  while (rem % 7 == 0) { radix[ns++] = 7; rem /= 7; }
+  while (e2 >= 3) { radix[ns++] = 8; e2 -= 3; }
+  return ns;
+}
+
+static double butterfly_cost(int r) {
+  switch (r) {
+    case 2: return 4;
+    case 3: return 12;
+    case 4: return 16;
+    case 5: return 36;
+    case 7: return 66;
+    case 8: return 56;
+  }
+  return 1e9;
+}
+
+double fft_cost(int n) {
+  int radix[kMaxStages];
+  int ns = radix_schedule(n, radix);
+  double c = 0;
+  for (int s = 0; s < ns; ++s) {
+    const int r = radix[s];
+    const double tw = (s + 1 < ns) ? 4.0 * (r - 1) : 0.0;
+    c += (double)(n / r) * (butterfly_cost(r) + tw);
+    c += 10.0 * n;  // one load + one store pass over shared memory, index arithmetic
+  }
+  return c;
+}
+
+static std::vector<int> period_candidates(int n_min) {
+  std::vector<int> v;
+  int p = next_smooth2357(n_min);
+  const int limit = n_min + n_min / 4 + 8;
+  while ((int)v.size() < 8 && (p <= limit || v.empty())) {
+    v.push_back(p);
+    p = next_smooth2357(p + 1);
+  }
+  return v;
+}
+
+int choose_period(int n_min) {
+  int best = 0;
+  double best_c = 0;
+  for (int p : period_candidates(n_min)) {
+    double c = fft_cost(p);
+    if (!best || c < best_c) { best = p; best_c = c; }
+  }
+  return best;
+}
+
+// factorize.h:71-90 -- `n % 4*4*4*2 == 0` is ((n%4)*32)==0 by C precedence: multiples of 4 rejected.
+static bool ref_is_optimal(int n) {
+  if (n % 4 * 4 * 4 * 2 == 0) return false;
+  if (n == 1) return false;
+  static const int f[] = {13, 11, 7, 5, 3, 2, 0};
+  int ntest = n, last = 0;
+  for (int i = 0; f[i] && ntest != 1; ++i)
+    while (ntest % f[i] == 0) { ntest /= f[i]; last = f[i]; }
+  if (ntest != 1) last = ntest;
+  for (int i = 0; f[i]; ++i)
+    if (last == f[i]) return true;
+  return false;
+}
+
+int ref_find_closest_factor(int n) {
+  if (ref_is_optimal(n)) return n;
+  int j = n + 1;
+  while (!ref_is_optimal(j)) ++j;
+  return j;
+}
+
+static void finish_axis(AxisPlan& a) {
+  a.nstages = radix_schedule(a.P, a.radix);
+}
+
+// Per-axis facts that do not depend on the chosen period.
+static void axis_for_mode(int mode, int ns, int nk, AxisPlan& a) {
+  a.n_src = ns;
+  a.n_ker = nk;
+  const int L = ns + nk - 1;  // full linear length
+  a.fold = 0;
+  a.kwrap = 0;  // 0 = wrap modulo the period (set after P is known)
+  switch (mode) {
+    case 0:  // LINEAR_FULL            convolution_fftw.h:54-60
+    case 6:  // CIRCULAR_FULL_UNPADDED :106-113
+    case 7:  // CIRCULAR_FULL          :114-121  (period == full length: no aliasing)
+      a.n_dst = L; a.off = 0; a.min_period = L; a.lin = L; break;
+    case 1:  // LINEAR_SAME_UNPADDED   :61-67
+    case 2:  // LINEAR_SAME            :68-74 ; crop offset int(hk/2.0) :238-239
+      a.n_dst = ns; a.off = nk / 2; a.min_period = ns + nk / 2; a.lin = a.off + ns; break;
+    case 3:  // LINEAR_VALID           :75-92 ; crop offset hk-1 :259-260
+      a.n_dst = ns - nk + 1; a.off = nk - 1; a.min_period = ns; a.lin = ns; break;
+    case 4:  // CIRCULAR_SAME          :93-98 (exact period ns)
+      a.n_dst = ns; a.off = 0;
+      if (is_smooth2357(ns)) {
+        a.exact = true;
+        a.min_period = ns; a.lin = ns;  // run at the exact period, kernel wraps modulo ns
+      } else {
+        // fold(linear result) modulo ns == circular convolution modulo ns
+        a.fold = ns; a.kwrap = ns;
+        const int nke = std::min(nk, ns);
+        a.min_period = ns + nke - 1; a.lin = ns + nke - 1;
+      }
+      break;
+    case 5:  // CIRCULAR_SAME_PADDED   :99-105 == top-left ns crop of the full linear result
+      a.n_dst = ns; a.off = 0; a.min_period = L; a.lin = ns; break;
+  }
+}
+
+bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
+  if (mode < 0 || mode > 7) return false;
+  out = Plan2D();
+  out.mode = mode;
+  if (hs < 1 || ws < 1 || hk < 1 || wk < 1) return false;
+  // reference sizes, informational
+  switch (mode) {
+    case 0: case 6: out.ref_h_fft = ref_find_closest_factor(hs + hk - 1); out.ref_w_fft = ref_find_closest_factor(ws + wk - 1); break;
+    case 1: out.ref_h_fft = hs + hk / 2; out.ref_w_fft = ws + wk / 2; break;
+    case 2: out.ref_h_fft = ref_find_closest_factor(hs + hk / 2); out.ref_w_fft = ref_find_closest_factor(ws + wk / 2); break;
+    case 3: out.ref_h_fft = ref_find_closest_factor(hs); out.ref_w_fft = ref_find_closest_factor(ws); break;
+    case 4: out.ref_h_fft = hs; out.ref_w_fft = ws; break;
+    case 5: out.ref_h_fft = ref_find_closest_factor(hs + hk); out.ref_w_fft = ref_find_closest_factor(ws + wk); break;
+    case 7: out.ref_h_fft = hs + hk - 1; out.ref_w_fft = ws + wk - 1; break;
+  }
+  if (mode == 3 && (hk > hs || wk > ws)) {  // convolution_fftw.h:77-84
+    out.empty = true;
+    out.ref_h_fft = out.ref_w_fft = 0;
+    out.h.n_src = hs; out.h.n_ker = hk; out.w.n_src = ws; out.w.n_ker = wk;
+    return true;
+  }
+  axis_for_mode(mode, hs, hk, out.h);
+  axis_for_mode(mode, ws, wk, out.w);
+
+  // Joint choice of (P_h, P_w): row passes touch (n_src + lin) lines of length P_w,
+  // column passes touch 2*P_w lines of length P_h.
+  std::vector<int> ch = period_candidates(out.h.min_period);
+  std::vector<int> cw = period_candidates(out.w.min_period);
+  if (out.h.exact) ch.assign(1, out.h.min_period);
+  if (out.w.exact) cw.assign(1, out.w.min_period);
+  double best = -1;
+  for (int ph : ch)
+    for (int pw : cw) {
+      const double rows = (double)std::min(ph, out.h.n_src) + std::min(ph, out.h.lin);
+      double c = rows * fft_cost(pw) + 2.0 * pw * fft_cost(ph) + 12.0 * ph * pw;
+      if (best < 0 || c < best) { best = c; out.h.P = ph; out.w.P = pw; }
+    }
+  for (AxisPlan* a : {&out.h, &out.w}) {
+    if (a->kwrap == 0) a->kwrap = a->P;
+    a->n_ker_eff = std::min(a->n_ker, a->kwrap);
+    a->lin = std::min(a->lin, a->P);
+    finish_axis(*a);
+  }
+  return true;
+}
+
+void dif_permutation(int n, int nstages, const int* radix, int* freq_of_pos) {
+  for (int pos = 0; pos < n; ++pos) {
+    int rem = pos, len = n, mult = 1, freq = 0;
+    for (int s = 0; s < nstages; ++s) {
+      const int m = len / radix[s];
+      const int p = rem / m;
+      rem -= p * m;
+      freq += p * mult;
+      mult *= radix[s];
+      len = m;
+    }
+    freq_of_pos[pos] = freq;
+  }
+}
+
+}  // namespace b2c

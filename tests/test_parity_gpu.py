@@ -1,0 +1,236 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the CPU oracle on the same seeded
+inputs, against the committed golden vectors, and -- at BASELINE.json's full sizes -- through
+size-independent properties.  Tolerance: 1e-12 relative L2 (BASELINE.json north_star) and the
+reference harness's 1e-10 absolute L2 (convolution_test.cc:49)."""
+import os
+
+import numpy as np
+import pytest
+
+import _oracle
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-12
+ABS_TOL = 1e-10
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden.npz"))
+CASES = [tuple(int(v) for v in row) for row in GOLD["cases"]]
+
+
+def _check(got, want, what):
+    assert got.shape == want.shape, (what, got.shape, want.shape)
+    if want.size == 0:
+        return
+    assert np.all(np.isfinite(got)), what
+    rel = _oracle.rel_err(got, want)
+    ab = float(np.linalg.norm((got - want).ravel()))
+    assert rel <= REL_TOL, (what, rel)
+    assert ab <= ABS_TOL * max(1.0, np.linalg.norm(want.ravel())), (what, ab)
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    torch.cuda.set_device(0)
+    return torch
+
+
+@pytest.mark.parametrize("ci", range(len(CASES)))
+@pytest.mark.parametrize("path", ["fft", "direct"])
+def test_single_call_matches_golden_all_modes(b2c, torch_cuda, ci, path):
+    hs, ws, hk, wk, seed = CASES[ci]
+    rng = np.random.default_rng(seed)
+    src, ker = rng.random((hs, ws)), rng.random((hk, wk))
+    for mode in range(8):
+        key = "c%d_m%d" % (ci, mode)
+        if key not in GOLD:
+            continue
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        p.set_path(b2c.PATH_FFT if path == "fft" else b2c.PATH_DIRECT)
+        try:
+            got = p.convolve_host(src, ker)
+        except b2c.B2CError as e:
+            if path == "direct" and e.code == 4:   # kernel too large for the direct tile: documented limit
+                p.destroy()
+                continue
+            raise
+        _check(got, GOLD[key], (path, b2c.MODE_NAMES[mode], CASES[ci]))
+        p.destroy()
+
+
+def _random_case(rng, kind):
+    # the reference test driver's nine size categories (convolution_test.cc:424-523)
+    u = lambda: rng.random()
+    if kind == 0: return 2 * int(20 * u() + 30), 1, 2 * int(20 * u() + 30), 1
+    if kind == 1: return 2 * int(20 * u() + 30), 1, 2 * int(20 * u() + 20) + 1, 1
+    if kind == 2: return 2 * int(20 * u() + 30) + 1, 1, int(20 * u() + 20), 1
+    if kind == 3: return 2 * int(20 * u() + 30) + 1, 1, int(20 * u() + 20) + 1, 1
+    if kind == 4: return 1, 2 * int(20 * u() + 30), 1, 2 * int(20 * u() + 20)
+    if kind == 5: return 1, 2 * int(20 * u() + 30), 1, 2 * int(20 * u() + 20) + 1
+    if kind == 6: return 1, 2 * int(20 * u() + 30) + 1, 1, int(20 * u() + 20)
+    if kind == 7: return 1, 2 * int(20 * u() + 30) + 1, 1, int(20 * u() + 20) + 1
+    return int(20 * u() + 30), int(20 * u() + 30), int(20 * u() + 20), int(20 * u() + 20)
+
+
+@pytest.mark.parametrize("kind", range(9))
+def test_reference_test_categories_vs_oracle(b2c, oracle, torch_cuda, kind):
+    """Seeded re-run of the reference's 9 categories x all 8 modes (it only pins 6 of them against
+    Octave); the oracle is the long-double nested-loop restatement."""
+    rng = np.random.default_rng(100 + kind)
+    for _ in range(6):
+        hs, ws, hk, wk = _random_case(rng, kind)
+        src, ker = rng.random((hs, ws)), rng.random((hk, wk))
+        for mode in range(8):
+            want = oracle.convolve_direct8(mode, src, ker)
+            ws_ = b2c.Workspace()
+            b2c.init_workspace(ws_, mode, hs, ws, hk, wk)
+            b2c.convolve(ws_, src, ker)
+            got = ws_.dst if ws_.dst is not None else np.zeros((0, 0))
+            _check(got.reshape(want.shape) if want.size == 0 else got, want, (b2c.MODE_NAMES[mode], hs, ws, hk, wk))
+            b2c.clear_workspace(ws_)
+
+
+def test_edge_sizes_vs_oracle(b2c, oracle, torch_cuda):
+    rng = np.random.default_rng(5)
+    shapes = [(1, 1, 1, 1), (1, 2, 1, 1), (2, 1, 3, 1), (3, 3, 3, 3), (3, 5, 7, 2), (8, 8, 1, 1), (5, 4, 5, 4),
+              (13, 11, 26, 23), (2, 100, 2, 99), (100, 2, 1, 2), (97, 89, 5, 3), (64, 64, 64, 64)]
+    for hs, ws, hk, wk in shapes:
+        src, ker = rng.random((hs, ws)), rng.random((hk, wk))
+        for mode in range(8):
+            want = oracle.convolve_direct8(mode, src, ker)
+            for path in (b2c.PATH_FFT, b2c.PATH_DIRECT):
+                p = b2c.Plan(mode, hs, ws, hk, wk)
+                p.set_path(path)
+                got = p.convolve_host(src, ker)
+                _check(got, want, (b2c.MODE_NAMES[mode], path, hs, ws, hk, wk))
+                p.destroy()
+
+
+def test_batch_device_shared_kernel_equals_single_calls(b2c, oracle, torch_cuda):
+    torch = torch_cuda
+    rng = np.random.default_rng(11)
+    for (hs, ws, hk, wk, mode, n) in [(50, 50, 10, 10, 2, 7), (100, 100, 15, 15, 2, 10), (33, 20, 12, 9, 0, 5),
+                                      (41, 1, 8, 1, 4, 9), (1, 77, 1, 30, 3, 4)]:
+        src = rng.random((n, hs, ws))
+        ker = rng.random((hk, wk))
+        for path in (b2c.PATH_FFT, b2c.PATH_DIRECT):
+            p = b2c.Plan(mode, hs, ws, hk, wk)
+            p.set_path(path)
+            d_src = torch.from_numpy(src).cuda()
+            d_ker = torch.from_numpy(ker).cuda()
+            d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n,
+                                    torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            got = d_dst.cpu().numpy()
+            for i in range(n):
+                _check(got[i], oracle.convolve_direct8(mode, src[i], ker), (path, mode, i))
+            p.destroy()
+
+
+def test_batch_device_per_image_kernels(b2c, oracle, torch_cuda):
+    torch = torch_cuda
+    rng = np.random.default_rng(12)
+    for (hs, ws, hk, wk, mode, n) in [(20, 20, 20, 20, 7, 5), (30, 25, 7, 9, 2, 4), (17, 1, 40, 1, 4, 3),
+                                      (1, 50, 1, 50, 0, 3), (25, 31, 6, 4, 3, 3), (100, 100, 100, 100, 7, 2)]:
+        src = rng.random((n, hs, ws))
+        ker = rng.random((n, hk, wk))
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        p.set_path(b2c.PATH_FFT)
+        d_src = torch.from_numpy(src).cuda()
+        d_ker = torch.from_numpy(ker).cuda()
+        d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+        p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 0, d_dst.data_ptr(), n, 0)
+        torch.cuda.synchronize()
+        got = d_dst.cpu().numpy()
+        for i in range(n):
+            _check(got[i], oracle.convolve_direct8(mode, src[i], ker[i]), (mode, i, hs, ws, hk, wk))
+        p.destroy()
+
+
+def test_config3_shape_and_circular_full_identity(b2c, oracle, torch_cuda):
+    """BASELINE config 3: 100x100 (*) 100x100 CIRCULAR_FULL, per-image kernels -> 199x199, equal to
+    LINEAR_FULL (period == full length)."""
+    rng = np.random.default_rng(13)
+    src, ker = rng.random((100, 100)), rng.random((100, 100))
+    a = b2c.Plan(b2c.CIRCULAR_FULL, 100, 100, 100, 100)
+    assert (a.h_dst, a.w_dst) == (199, 199)
+    got = a.convolve_host(src, ker)
+    _check(got, oracle.convolve_fftw(b2c.CIRCULAR_FULL, src, ker), "config3 vs reference FFT path restated")
+    b = b2c.Plan(b2c.LINEAR_FULL, 100, 100, 100, 100)
+    _check(b.convolve_host(src, ker), got, "LINEAR_FULL == CIRCULAR_FULL")
+
+
+def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
+    """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
+    rng = np.random.default_rng(14)
+    for n, m in [(63, 16), (64, 15), (255, 256), (1000, 3), (4095, 4), (4096, 255), (4096, 4097)]:
+        src, ker = rng.random((1, n)), rng.random((1, m))
+        for mode in range(8):
+            want = oracle.convolve_direct8(mode, src, ker)
+            p = b2c.Plan(mode, 1, n, 1, m)
+            _check(p.convolve_host(src, ker), want, ("1xN", mode, n, m))
+            p.destroy()
+            p = b2c.Plan(mode, n, 1, m, 1)
+            _check(p.convolve_host(src.T.copy(), ker.T.copy()), want.T, ("Nx1", mode, n, m))
+            p.destroy()
+
+
+def test_host_batch_pipeline_matches_device_batch(b2c, oracle, torch_cuda):
+    rng = np.random.default_rng(15)
+    n, hs, ws, hk, wk = 1500, 100, 100, 15, 15   # > one pipeline chunk
+    src = rng.random((n, hs, ws))
+    ker = rng.random((hk, wk))
+    p = b2c.Plan(b2c.LINEAR_SAME, hs, ws, hk, wk)
+    got = p.convolve_batch_host(src, ker)
+    for i in [0, 1, 2, 599, 600, 1198, 1199, 1499]:
+        _check(got[i], oracle.convolve_direct8(b2c.LINEAR_SAME, src[i], ker), ("host pipeline", i))
+    # linearity over the whole batch: conv(sum_i a_i) == sum_i conv(a_i)
+    total = p.convolve_host(src.sum(axis=0), ker)
+    assert _oracle.rel_err(got.sum(axis=0), total) <= 1e-11
+    pk = rng.random((n, hk, wk))
+    got2 = p.convolve_batch_host(src[:40], pk[:40])
+    for i in [0, 17, 39]:
+        _check(got2[i], oracle.convolve_direct8(b2c.LINEAR_SAME, src[i], pk[i]), ("host per-image", i))
+
+
+def test_headline_full_size_properties(b2c, oracle, torch_cuda):
+    """BASELINE config 2 at full size (65536 x 100x100 (*) 15x15 LINEAR_SAME, device resident):
+    spot-check images against the oracle, commutation with a delta kernel, linearity, and equality of
+    the checksum of the batch with the checksum of its two halves run separately."""
+    torch = torch_cuda
+    n, hs, ws, hk, wk = 65536, 100, 100, 15, 15
+    seed = 0x5EED0002
+    d_src = torch.empty((n, hs, ws), dtype=torch.float64, device="cuda")
+    b2c.fill_uniform_device(d_src.data_ptr(), d_src.numel(), seed)
+    torch.cuda.synchronize()
+    host_first = d_src[:3].cpu().numpy()
+    assert np.array_equal(host_first.ravel(), _oracle.splitmix_uniform(seed, 0, 3 * hs * ws))
+    ker = np.random.default_rng(16).random((hk, wk))
+    d_ker = torch.from_numpy(ker).cuda()
+    d_dst = torch.empty((n, hs, ws), dtype=torch.float64, device="cuda")
+    p = b2c.Plan(b2c.LINEAR_SAME, hs, ws, hk, wk)
+    p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+    torch.cuda.synchronize()
+    for i in [0, 1, 2, 12345, 65534, 65535]:
+        img = _oracle.splitmix_uniform(seed, i * hs * ws, hs * ws).reshape(hs, ws)
+        _check(d_dst[i].cpu().numpy(), oracle.convolve_direct8(b2c.LINEAR_SAME, img, ker), ("headline", i))
+    whole = b2c.checksum_device(d_dst.data_ptr(), d_dst.numel())
+    # halves, as two ranks would own them: checksums add up
+    b0, e0 = b2c.partition(n, 2, 0)
+    b1, e1 = b2c.partition(n, 2, 1)
+    d_half = torch.empty((e0 - b0, hs, ws), dtype=torch.float64, device="cuda")
+    parts = []
+    for b, e in [(b0, e0), (b1, e1)]:
+        p.convolve_batch_device(d_src[b:e].data_ptr(), d_ker.data_ptr(), 1, d_half.data_ptr(), e - b, 0)
+        torch.cuda.synchronize()
+        parts.append(b2c.checksum_device(d_half.data_ptr(), (e - b) * hs * ws))
+    assert (parts[0][0] + parts[1][0]) % (1 << 64) == whole[0]
+    assert parts[0][1] ^ parts[1][1] == whole[1]
+    # delta kernel centred like LINEAR_SAME's crop: identity
+    delta = np.zeros((hk, wk)); delta[hk // 2, wk // 2] = 1.0
+    d_delta = torch.from_numpy(delta).cuda()
+    p.convolve_batch_device(d_src.data_ptr(), d_delta.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+    torch.cuda.synchronize()
+    assert float((d_dst - d_src).abs().max()) < 1e-13
