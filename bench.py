@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 convolution engine (BASELINE.json metric).
+
+Workload (BASELINE.json configs[1]): batched 2-D LINEAR_SAME, 65536 images 100x100 (*) one shared
+15x15 kernel, FP64, per GPU.  A "step" is one pass of the hot path over that batch:
+kernel-spectrum kernel + fused convolution kernel (b2c_convolve_batch_device).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # this engine
+  python bench.py --impl reference [...]                         # reference CPU path on host cores
+  torchrun ... bench.py --gpus N ...                             # one rank per GPU, weak scaling
+
+Prints ONE JSON line (rank 0).  Numbers:
+  value     conv/s, inputs resident in HBM, CUDA events on the launching stream, max over ranks
+  e2e       conv/s through b2c_convolve_batch_host with pinned HOST buffers (H2D + D2H inside)
+  roofline  dominant kernel vs the measured HBM copy bandwidth (MEASURED_PEAKS.json)
+  cpu_baseline  the reference's convolution_fftw.h (unmodified, over the stand-in FFT) on all host cores
+The oracle/reference libraries are used here ONLY as the timed CPU baseline, never on the GPU path.
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+H = W = 100
+HK = WK = 15
+MODE_LINEAR_SAME = 2
+BATCH = 65536
+SEED = 0x5EED0002
+ALGO_BYTES_PER_CONV = (H * W + H * W) * 8  # 80 000 read + 80 000 written
+METRIC = "2D conv/s (f64, 100x100 (*) 15x15 LINEAR_SAME batch)"
+UNIT = "conv/s"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(path))["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def ncu_traffic():
+    """dram bytes read+written per launch of the dominant kernel from the committed ncu capture."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))["traffic_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons of one GPU during the timed region (NVML, ~5 ms period)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self.stop_flag = False
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.nv = None
+
+    def sample(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+                     0x4: "sw_power_cap", 0x80: "hw_power_brake", 0x2: "applications_clocks_setting"}
+            for bit, name in names.items():
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def run(self):
+        while not self.stop_flag:
+            self.sample()
+            time.sleep(0.005)
+
+    def result(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+def reference_batch_fn():
+    """(callable, kind): the reference CPU implementation of the path for a batch of images."""
+    import _oracle
+    ref = _oracle.load_ref()
+    if ref is not None:
+        return ref, "reference"
+    return _oracle.load_oracle(), "port"
+
+
+def time_cpu_reference(n_sample, threads, reps=1):
+    import numpy as np
+    import _oracle
+    lib, kind = reference_batch_fn()
+    src = _oracle.splitmix_uniform(SEED, 0, n_sample * H * W).reshape(n_sample, H, W)
+    ker = np.random.default_rng(SEED).random((HK, WK))
+    best = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        lib.batch_fftw(MODE_LINEAR_SAME, src, ker, threads=threads)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return n_sample / best, kind, best
+
+
+def cpu_sample_size(threads, target_s):
+    """Calibrate a bounded sample (about target_s seconds of CPU work on `threads` threads)."""
+    rate, _, _ = time_cpu_reference(4 * threads, threads)
+    n = int(max(4 * threads, min(BATCH, rate * target_s)))
+    return n
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = host_cores()
+    n_sample = cpu_sample_size(cores, 2.0)
+    for _ in range(min(args.warmup, 1)):
+        time_cpu_reference(n_sample, cores)
+    times = []
+    kind = None
+    for _ in range(args.steps):
+        rate, kind, dt = time_cpu_reference(n_sample, cores)
+        times.append(dt)
+    total = sum(times)
+    value = n_sample * args.steps / total
+    sample = "%d of %d images per step, convolution_fftw.h %s, %d threads each with its own Workspace" % (
+        n_sample, BATCH, "unmodified over stand-in FFT (no libfftw3 on box)" if kind == "reference" else "restated (oracle port)",
+        cores)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "configs[1]: 65536 x 100x100 (*) shared 15x15 LINEAR_SAME f64 (bounded sample per step)",
+                   "batch_per_step": n_sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b2c_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import fftconvolution_b200 as b2c
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    b2c.lib().b2c_set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n_local = args.batch                      # weak scaling: every GPU owns a full 65536-image shard
+    n_global = n_local * world
+    first, _ = b2c.partition(n_global, world, rank)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    d_src = torch.empty((n_local, H, W), dtype=torch.float64, device="cuda")
+    d_dst = torch.empty((n_local, H, W), dtype=torch.float64, device="cuda")
+    b2c.fill_uniform_device(d_src.data_ptr(), d_src.numel(), SEED, first * H * W, stream)
+    ker = np.random.default_rng(SEED).random((HK, WK))
+    d_ker = torch.from_numpy(ker).cuda()
+    plan = b2c.Plan(b2c.LINEAR_SAME, H, W, HK, WK)
+
+    def step():
+        plan.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n_local, stream)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    sampler = ClockSampler(local_rank)
+    L = b2c.lib()
+    L.b2c_kernel_timer(1)
+    launches0 = L.b2c_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    sampler.sample()
+    barrier()
+    sampler.sample()
+    sampler.stop_flag = True
+    elapsed_ms = ev0.elapsed_time(ev1)
+    launches = L.b2c_launch_count() - launches0
+    avg_ms, nl = ctypes.c_double(), ctypes.c_long()
+    L.b2c_kernel_timer_read(ctypes.byref(avg_ms), ctypes.byref(nl))
+    L.b2c_kernel_timer(0)
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(t.item())
+    value = n_global * args.steps / (elapsed_ms * 1e-3)
+
+    # verification checksum of the sharded result: wrapping sum of bit patterns, all-reduced
+    cs = b2c.checksum_device(d_dst.data_ptr(), d_dst.numel(), stream)
+    cs_t = torch.tensor([cs[0] & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(cs_t, op=dist.ReduceOp.SUM)
+
+    # ---- end to end: pinned host buffers through the C-ABI host entry point
+    e2e = None
+    try:
+        if args.no_e2e:
+            raise RuntimeError("skipped (--no-e2e)")
+        n_e2e = args.e2e_batch
+        src_bytes, dst_bytes = n_e2e * H * W * 8, n_e2e * H * W * 8
+        h_src = torch.empty((n_e2e, H, W), dtype=torch.float64).pin_memory()
+        h_dst = torch.empty((n_e2e, H, W), dtype=torch.float64).pin_memory()
+        h_src.copy_(d_src[:n_e2e])
+        h_ker = torch.from_numpy(ker).pin_memory()
+        e_steps = max(1, min(args.steps, 3))
+        plan.convolve_batch_host_ptr(h_src.data_ptr(), h_ker.data_ptr(), 1, h_dst.data_ptr(), n_e2e)  # warm
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            plan.convolve_batch_host_ptr(h_src.data_ptr(), h_ker.data_ptr(), 1, h_dst.data_ptr(), n_e2e)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        ok = bool(torch.equal(h_dst[:64], d_dst[:64].cpu()))
+        e2e = {"value": n_e2e * world * e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": src_bytes + HK * WK * 8,
+               "d2h_bytes_per_step": dst_bytes, "batch_per_gpu": n_e2e, "steps": e_steps,
+               "matches_device_path": ok}
+        del h_src, h_dst
+    except Exception as ex:  # pinned allocation can fail on a small host; say so instead of faking a number
+        e2e = {"value": None, "unit": UNIT, "error": str(ex)[:200]}
+
+    peak, peak_kind = measured_peak()
+    kernel_s = avg_ms.value * 1e-3
+    achieved = (n_local * ALGO_BYTES_PER_CONV / kernel_s) / 1e9 if kernel_s > 0 else None
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(),
+                "peak_kind": peak_kind, "kernel": "conv_shared_kernel", "kernel_ms": avg_ms.value,
+                "kernel_launches": nl.value, "algorithmic_bytes_per_launch": n_local * ALGO_BYTES_PER_CONV}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = host_cores()
+        n_sample = cpu_sample_size(cores, 12.0)
+        rate, kind, dt = time_cpu_reference(n_sample, cores)
+        cpu_baseline = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+                        "sample": "%d of %d images, convolution_fftw.h %s, %d threads (%.1f s)" % (
+                            n_sample, BATCH,
+                            "unmodified over stand-in FFT (no libfftw3 on box)" if kind == "reference" else "restated (oracle port)",
+                            cores, dt)}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "configs[1]: 65536 x 100x100 (*) shared 15x15 LINEAR_SAME f64, per GPU",
+                       "batch_per_gpu": n_local, "fft_period": [plan.h_fft, plan.w_fft],
+                       "l2": "inputs 5.24 GB + outputs 5.24 GB per GPU, far larger than the 126 MB L2 (no flush needed)",
+                       "rng": "splitmix64 seed 0x5EED0002 on device"},
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": sampler.result(), "checksum_sum63": int(cs_t.item()),
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b2c", choices=["b2c", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--e2e-batch", type=int, default=BATCH)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_b2c_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

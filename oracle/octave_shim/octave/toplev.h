@@ -1,0 +1,2 @@
+// TEST INFRASTRUCTURE ONLY -- see oct.h in this directory.
+#include "oct.h"
