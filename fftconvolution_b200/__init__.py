@@ -22,6 +22,7 @@ from .capi import (  # noqa: F401
     PATH_AUTO,
     PATH_FFT,
     PATH_DIRECT,
+    PATH_FFT_GENERIC,
 )
 from .convolution import (  # noqa: F401
     Plan,

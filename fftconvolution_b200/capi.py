@@ -15,7 +15,7 @@ MODE_NAMES = [
     "LINEAR_FULL", "LINEAR_SAME_UNPADDED", "LINEAR_SAME", "LINEAR_VALID",
     "CIRCULAR_SAME", "CIRCULAR_SAME_PADDED", "CIRCULAR_FULL_UNPADDED", "CIRCULAR_FULL",
 ]
-PATH_AUTO, PATH_FFT, PATH_DIRECT = 0, 1, 2
+PATH_AUTO, PATH_FFT, PATH_DIRECT, PATH_FFT_GENERIC = 0, 1, 2, 3
 
 # every symbol include/b2conv.h declares -- tests/test_abi.py checks the header against this list
 SYMBOLS = [

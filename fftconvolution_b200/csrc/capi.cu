@@ -28,6 +28,13 @@ int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
 int occupancy_direct(size_t smem);
+// conv_tuned108.cu
+size_t tuned108_smem_bytes();
+size_t tuned108_kspec_bytes();
+int tuned108_occupancy();
+cudaError_t launch_tuned108_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st);
+cudaError_t launch_tuned108_conv(int hs, int ws, int hd, int wd, int off_h, int off_w, const double* d_src,
+                                 double* d_dst, long n, const cplx* kspec, const cplx* tw, int grid, cudaStream_t st);
 // util_kernels.cu
 cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long first, cudaStream_t st);
 cudaError_t launch_checksum(const double* d, long n, unsigned long long* d_out3, cudaStream_t st);
@@ -191,10 +198,38 @@ void fill_axis(AxisDev& d, const AxisPlan& a, const AxisTables& t) {
   d.neg = t.neg;
 }
 
+// Shared-kernel plans whose periods are 108 x 108 run on the tuned kernel (conv_tuned108.cu).
+bool tuned108_applies(const b2c_plan* p, int shared) {
+  const Plan2D& pl = p->pl;
+  return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == 108 && pl.w.P == 108 &&
+         pl.h.fold == 0 && pl.w.fold == 0 && pl.h.kwrap == 108 && pl.w.kwrap == 108;
+}
+
+int run_tuned108(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
+  const Plan2D& pl = p->pl;
+  if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, work_bytes(pl)));
+  CUDA_TRY(launch_tuned108_kspec(d_ker, pl.h.n_ker, pl.w.n_ker, p->tw.tw, p->kspec, st));
+  ++g_launches;
+  const int occ = tuned108_occupancy();
+  if (occ < 1) return fail(B2C_ECUDA, "tuned 108x108 kernel cannot be resident");
+  int grid = (int)std::min<long>(n, (long)p->ctx->sms * occ);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_timer.on && g_timer.ev.size() < 8192) {
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, st));
+  }
+  CUDA_TRY(launch_tuned108_conv(pl.h.n_src, pl.w.n_src, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off, d_src, d_dst,
+                                n, p->kspec, p->tw.tw, grid, st));
+  ++g_launches;
+  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  return 0;
+}
+
 int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst,
                  long n, cudaStream_t st) {
   if (int rc = ensure_device_state(p)) return rc;
   const Plan2D& pl = p->pl;
+  if (tuned108_applies(p, shared)) return run_tuned108(p, d_src, d_ker, d_dst, n, st);
   ConvParams q;
   memset(&q, 0, sizeof q);
   q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
@@ -367,7 +402,7 @@ int b2c_plan_info(const b2c_plan* p, int* path, int* off_h, int* off_w, int* fol
 }
 
 int b2c_plan_set_path(b2c_plan* p, int path) {
-  if (!p || path < 0 || path > 2) return fail(B2C_EINVAL, "b2c_plan_set_path: bad arguments");
+  if (!p || path < 0 || path > 3) return fail(B2C_EINVAL, "b2c_plan_set_path: bad arguments");
   p->forced_path = path;
   return 0;
 }

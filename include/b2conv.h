@@ -33,7 +33,8 @@ enum {
 enum { B2C_OK = 0, B2C_EINVAL = 1, B2C_ECUDA = 2, B2C_ENOMEM = 3, B2C_ESIZE = 4 };
 
 /* Compute path selection (b2c_plan_set_path). AUTO = planner's measured crossover. */
-enum { B2C_PATH_AUTO = 0, B2C_PATH_FFT = 1, B2C_PATH_DIRECT = 2 };
+/* FFT_GENERIC = the any-size FFT kernel even where a tuned kernel exists (tests, comparisons). */
+enum { B2C_PATH_AUTO = 0, B2C_PATH_FFT = 1, B2C_PATH_DIRECT = 2, B2C_PATH_FFT_GENERIC = 3 };
 
 typedef struct b2c_plan b2c_plan;
 

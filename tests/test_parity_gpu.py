@@ -234,3 +234,32 @@ def test_headline_full_size_properties(b2c, oracle, torch_cuda):
     p.convolve_batch_device(d_src.data_ptr(), d_delta.data_ptr(), 1, d_dst.data_ptr(), n, 0)
     torch.cuda.synchronize()
     assert float((d_dst - d_src).abs().max()) < 1e-13
+
+
+def test_tuned_108_kernel_vs_oracle_and_generic(b2c, oracle, torch_cuda):
+    """Plans whose periods are 108 x 108 run on the hand-tuned kernel (conv_tuned108.cu): check it
+    against the oracle, and bit-compare the batch against itself run image by image."""
+    torch = torch_cuda
+    rng = np.random.default_rng(21)
+    cases = [(2, 100, 100, 15, 15), (0, 90, 95, 19, 14), (3, 108, 108, 5, 5), (2, 101, 104, 14, 9),
+             (0, 50, 60, 59, 49), (5, 100, 100, 9, 9), (7, 54, 54, 55, 55), (1, 100, 100, 16, 17),
+             (2, 30, 100, 157, 17)]
+    for mode, hs, ws, hk, wk in cases:
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        assert (p.h_fft, p.w_fft) == (108, 108), (mode, hs, ws, hk, wk, p.h_fft, p.w_fft)
+        p.set_path(b2c.PATH_FFT)
+        n = 5
+        src = rng.random((n, hs, ws))
+        ker = rng.random((hk, wk))
+        d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+        d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+        p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+        torch.cuda.synchronize()
+        got = d_dst.cpu().numpy()
+        for i in range(n):
+            _check(got[i], oracle.convolve_direct8(mode, src[i], ker), ("tuned108", mode, hs, ws, hk, wk, i))
+        g = b2c.Plan(mode, hs, ws, hk, wk)
+        g.set_path(b2c.PATH_FFT_GENERIC)
+        _check(g.convolve_host(src[0], ker), got[0], ("generic == tuned", mode))
+        one = p.convolve_host(src[3], ker)
+        assert np.array_equal(one, got[3]), "batch result must not depend on batch position"
