@@ -2,21 +2,24 @@
 // headline workload gets (100x100 (*) 15x15 LINEAR_SAME needs a period >= 107).
 // Replaces fftw_circular_convolution + crop (reference convolution_fftw.h:169-284) for that plan.
 //
-// One CTA owns one image; two CTAs are resident per SM (97.6 KB of shared memory each), so one
-// loads/stores while the other computes.  Data flow, all in ONE shared buffer Z[54][113] complex:
-//   1 rows  fwd radix-12 : global -> Z.  Rows r and r+54 ride one complex transform
-//                          (z = x_r + i*x_{r+54}); zero padding happens in registers.
-//   2 rows  fwd radix-9
-//   3 cols  fwd radix-12 : Hermitian unpack of the two packed rows in registers, then butterfly.
-//                          Only 55 of the 108 columns exist (real input => half spectrum).
-//   4 cols  radix-9 fwd, * cached kernel spectrum (1/N folded in), radix-9 bwd -- one pass.
-//   5 cols  bwd radix-12 : butterfly, then repack rows r / r+54 into one complex row.
-//   6 rows  bwd radix-9
-//   7 rows  bwd radix-12 : Z -> global, cropping to the output window in registers.
+// One CTA owns one image; two CTAs are resident per SM (99.4 KB of shared memory each), so one
+// loads/stores while the other computes.  The image is transformed VERTICALLY first so that the
+// lanes of a warp walk adjacent image columns: global loads and stores are coalesced.
+// Data flow, all in ONE shared buffer Z[54][115] complex ("line" = a pair of image columns):
+//   1 vert. fwd radix-12 : global -> Z.  Columns c and c+54 ride one complex transform
+//                          (z = x_c + i*x_{c+54}); zero padding happens in registers.
+//   2 vert. fwd radix-9
+//   3 horiz fwd radix-12 : Hermitian unpack of the two packed columns in registers, then butterfly.
+//                          Only 55 of the 108 vertical frequencies exist (real input).
+//   4 horiz radix-9 fwd, * cached kernel spectrum (1/N folded in), radix-9 bwd -- one pass.
+//   5 horiz bwd radix-12 : butterfly, then repack columns c / c+54 into one complex line.
+//   6 vert. bwd radix-9
+//   7 vert. bwd radix-12 : Z -> global, cropping to the output window in registers.
 // Every pass is in place: a task reads and writes the same slots, so a single __syncthreads()
-// separates passes (6 per image).  Lane -> slot maps are chosen with LD = 113 (== 1 mod 8) so
-// 128-bit shared accesses of a quarter warp fall into distinct bank groups in every pass.
-// The 11 twiddles a thread needs (w108^(j*p), j fixed per thread) live in registers.
+// separates passes (6 per image).  In every pass adjacent lanes own adjacent LINES (stride
+// LD = 115, odd) or adjacent columns of Z, so 128-bit shared accesses of a quarter warp fall into
+// distinct bank groups.  The 11 twiddles a thread needs (w108^(j*p), j fixed per thread) live in
+// registers.
 #include "conv_params.h"
 
 namespace b2c {
@@ -27,18 +30,17 @@ namespace t108 {
 
 constexpr int P = 108;
 constexpr int HALF = 54;
-constexpr int LD = 113;
+constexpr int LD = 115;          // odd stride (bank groups), chosen with tools/bank_sim_t108.py
 constexpr int NK = 55;          // half-spectrum columns
 constexpr int THREADS = 256;
-constexpr int A_LINES = 28;     // radix-12 passes: 9 tasks per line, 252 active threads
-constexpr int B_LINES = 21;     // radix-9  passes: 12 tasks per line, 252 active threads
+constexpr int A_LINES = 28;     // radix-12 passes: 28 lines x 9 butterflies = 252 active threads per round
 
 struct Params {
   int hs, ws, hd, wd, off_h, off_w;
   const double* src;
   double* dst;
   long n_images;
-  const cplx* kspec;  // [NK][P]: (half-spectrum column kk, scrambled row position)
+  const cplx* kspec;  // [P][NK]: (scrambled horizontal position, half-spectrum vertical frequency kk)
   const cplx* tw;     // exp(-2 pi i k / 108)
 };
 
@@ -106,33 +108,39 @@ __device__ __forceinline__ void swap_all(cplx* v) {
 __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant__ Params p) {
   cplx* Z = reinterpret_cast<cplx*>(b2c_smem_t108);
   const int t = threadIdx.x;
-  const bool act = t < 252;
-  const int la = t / 9, j = t - la * 9;     // radix-12 passes
-  const int lb = t / 12, pb = t - lb * 12;  // radix-9 passes
+  const bool act = t < 9 * A_LINES;
+  const int j = t / A_LINES, la = t - j * A_LINES;   // radix-12 passes: lanes walk adjacent lines
   cplx tw[12];
 #pragma unroll
-  for (int q = 1; q < 12; ++q) tw[q] = __ldg(&p.tw[j * q]);
+  for (int q = 1; q < 12; ++q) tw[q] = __ldg(&p.tw[(act ? j : 0) * q]);
 
   const size_t src_sz = (size_t)p.hs * p.ws, dst_sz = (size_t)p.hd * p.wd;
   for (long img = blockIdx.x; img < p.n_images; img += gridDim.x) {
     const double* __restrict__ x = p.src + (size_t)img * src_sz;
     double* __restrict__ y = p.dst + (size_t)img * dst_sz;
 
-    // ---- pass 1: rows, forward radix-12, global -> Z
+    // next image of this CTA -> L2 while this one is being transformed (one bulk prefetch, no registers)
+    if (t == 0 && img + gridDim.x < p.n_images) {
+      const double* nx = p.src + (size_t)(img + gridDim.x) * src_sz;
+      const unsigned bytes = (unsigned)((src_sz * sizeof(double)) & ~(size_t)15);
+      if ((reinterpret_cast<size_t>(nx) & 15) == 0 && bytes >= 16)   // bulk operations need 16-byte alignment
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nx), "r"(bytes) : "memory");
+    }
+
+    // ---- pass 1: vertical forward radix-12, global -> Z (image columns `line` and `line + 54`)
 #pragma unroll 1
     for (int rnd = 0; rnd < 2; ++rnd) {
       const int line = rnd * A_LINES + la;
       if (act && line < HALF) {
-        const bool r0 = line < p.hs, r1 = line + HALF < p.hs;
-        const double* x0 = x + (size_t)line * p.ws;
-        const double* x1 = x + (size_t)(line + HALF) * p.ws;
+        const bool c0 = line < p.ws, c1 = line + HALF < p.ws;
+        const double* xr = x + j * p.ws + line;
+        const int step = 9 * p.ws;
         cplx v[12];
 #pragma unroll
         for (int q = 0; q < 12; ++q) {
-          const int c = j + 9 * q;
-          const bool in = c < p.ws;
-          v[q].x = (in && r0) ? __ldg(x0 + c) : 0.0;
-          v[q].y = (in && r1) ? __ldg(x1 + c) : 0.0;
+          const bool in = j + 9 * q < p.hs;
+          v[q].x = (in && c0) ? __ldg(xr + q * step) : 0.0;
+          v[q].y = (in && c1) ? __ldg(xr + q * step + HALF) : 0.0;
         }
         bfly12(v);
         cplx* z = Z + line * LD + j;
@@ -143,23 +151,21 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
     }
     __syncthreads();
 
-    // ---- pass 2: rows, forward radix-9
+    // ---- pass 2: vertical forward radix-9 (task = block pb of line `line`)
 #pragma unroll 1
-    for (int rnd = 0; rnd < 3; ++rnd) {
-      const int line = rnd * B_LINES + lb;
-      if (act && line < HALF) {
-        cplx* z = Z + line * LD + 9 * pb;
-        cplx v[9];
+    for (int task = t; task < 12 * HALF; task += THREADS) {
+      const int pb = task / HALF, line = task - pb * HALF;
+      cplx* z = Z + line * LD + 9 * pb;
+      cplx v[9];
 #pragma unroll
-        for (int s = 0; s < 9; ++s) v[s] = z[s];
-        bfly9(v);
+      for (int s = 0; s < 9; ++s) v[s] = z[s];
+      bfly9(v);
 #pragma unroll
-        for (int s = 0; s < 9; ++s) z[s] = v[s];
-      }
+      for (int s = 0; s < 9; ++s) z[s] = v[s];
     }
     __syncthreads();
 
-    // ---- pass 3: columns, Hermitian unpack + forward radix-12
+    // ---- pass 3: horizontal, Hermitian unpack + forward radix-12
 #pragma unroll 1
     for (int rnd = 0; rnd < 2; ++rnd) {
       const int kk = rnd * A_LINES + la;
@@ -173,8 +179,8 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
         for (int q = 0; q < 6; ++q) {
           const cplx z1 = zr[9 * q * LD];
           const cplx z2 = self ? z1 : zp[9 * q * LD];
-          v[q] = make_double2(z1.x + z2.x, z1.y - z2.y);          // 2 * FFT(row r)     at this column
-          v[q + 6] = make_double2(z1.y + z2.y, z2.x - z1.x);      // 2 * FFT(row r + 54)
+          v[q] = make_double2(z1.x + z2.x, z1.y - z2.y);          // 2 * FFT(column c)      at this frequency
+          v[q + 6] = make_double2(z1.y + z2.y, z2.x - z1.x);      // 2 * FFT(column c + 54)
         }
         bfly12(v);
         zr[0] = v[0];
@@ -186,28 +192,26 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
     }
     __syncthreads();
 
-    // ---- pass 4: columns, radix-9 forward, spectrum product, radix-9 backward
+    // ---- pass 4: horizontal radix-9 forward, spectrum product, radix-9 backward
 #pragma unroll 1
-    for (int rnd = 0; rnd < 3; ++rnd) {
-      const int kk = rnd * B_LINES + lb;
-      if (act && kk < NK) {
-        const int col = pb < 6 ? rep_of(kk) : par_of(kk);
-        cplx* z = Z + (9 * (pb < 6 ? pb : pb - 6)) * LD + col;
-        const cplx* __restrict__ ks = p.kspec + kk * P + 9 * pb;
-        cplx v[9];
+    for (int task = t; task < 12 * NK; task += THREADS) {
+      const int pb = task / NK, kk = task - pb * NK;
+      const int col = pb < 6 ? rep_of(kk) : par_of(kk);
+      cplx* z = Z + (9 * (pb < 6 ? pb : pb - 6)) * LD + col;
+      const cplx* __restrict__ ks = p.kspec + (9 * pb) * NK + kk;
+      cplx v[9];
 #pragma unroll
-        for (int s = 0; s < 9; ++s) v[s] = z[s * LD];
-        bfly9(v);
+      for (int s = 0; s < 9; ++s) v[s] = z[s * LD];
+      bfly9(v);
 #pragma unroll
-        for (int s = 0; s < 9; ++s) v[s] = cswap(cmul(v[s], __ldg(ks + s)));   // product, swapped for the inverse
-        bfly9(v);
+      for (int s = 0; s < 9; ++s) v[s] = cswap(cmul(v[s], __ldg(ks + s * NK)));   // product, swapped for the inverse
+      bfly9(v);
 #pragma unroll
-        for (int s = 0; s < 9; ++s) z[s * LD] = cswap(v[s]);
-      }
+      for (int s = 0; s < 9; ++s) z[s * LD] = cswap(v[s]);
     }
     __syncthreads();
 
-    // ---- pass 5: columns, backward radix-12, repack two real rows into one complex row
+    // ---- pass 5: horizontal backward radix-12, repack two real columns into one complex line
 #pragma unroll 1
     for (int rnd = 0; rnd < 2; ++rnd) {
       const int kk = rnd * A_LINES + la;
@@ -234,23 +238,21 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
     }
     __syncthreads();
 
-    // ---- pass 6: rows, backward radix-9
+    // ---- pass 6: vertical backward radix-9
 #pragma unroll 1
-    for (int rnd = 0; rnd < 3; ++rnd) {
-      const int line = rnd * B_LINES + lb;
-      if (act && line < HALF) {
-        cplx* z = Z + line * LD + 9 * pb;
-        cplx v[9];
+    for (int task = t; task < 12 * HALF; task += THREADS) {
+      const int pb = task / HALF, line = task - pb * HALF;
+      cplx* z = Z + line * LD + 9 * pb;
+      cplx v[9];
 #pragma unroll
-        for (int s = 0; s < 9; ++s) v[s] = cswap(z[s]);
-        bfly9(v);
+      for (int s = 0; s < 9; ++s) v[s] = cswap(z[s]);
+      bfly9(v);
 #pragma unroll
-        for (int s = 0; s < 9; ++s) z[s] = cswap(v[s]);
-      }
+      for (int s = 0; s < 9; ++s) z[s] = cswap(v[s]);
     }
     __syncthreads();
 
-    // ---- pass 7: rows, backward radix-12, crop, Z -> global
+    // ---- pass 7: vertical backward radix-12, crop, Z -> global
 #pragma unroll 1
     for (int rnd = 0; rnd < 2; ++rnd) {
       const int line = rnd * A_LINES + la;
@@ -260,16 +262,18 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
         v[0] = cswap(z[0]);
 #pragma unroll
         for (int q = 1; q < 12; ++q) v[q] = cswap(cmulc(z[9 * q], tw[q]));
-        bfly12(v);   // results: re/im swapped => v[q].y is row `line`, v[q].x is row `line + 54`
-        const int i0 = line - p.off_h, i1 = line + HALF - p.off_h;
-        const bool o0 = i0 >= 0 && i0 < p.hd, o1 = i1 >= 0 && i1 < p.hd;
-        const long b0 = (long)i0 * p.wd - p.off_w, b1 = (long)i1 * p.wd - p.off_w;
+        bfly12(v);   // results: re/im swapped => v[q].y is column `line`, v[q].x is column `line + 54`
+        const int j0 = line - p.off_w, j1 = line + HALF - p.off_w;
+        const bool o0 = j0 >= 0 && j0 < p.wd, o1 = j1 >= 0 && j1 < p.wd;
+        const int i0 = j - p.off_h;
+        double* yr = y + i0 * p.wd + j0;
+        const int step = 9 * p.wd;
 #pragma unroll
         for (int q = 0; q < 12; ++q) {
-          const int c = j + 9 * q;
-          const bool in = c >= p.off_w && c < p.off_w + p.wd;
-          if (in && o0) y[b0 + c] = v[q].y;
-          if (in && o1) y[b1 + c] = v[q].x;
+          const unsigned i = (unsigned)(i0 + 9 * q);
+          const bool in = i < (unsigned)p.hd;
+          if (in && o0) yr[q * step] = v[q].y;
+          if (in && o1) yr[q * step + HALF] = v[q].x;
         }
       }
     }
@@ -277,21 +281,22 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
   }
 }
 
-// Kernel spectrum in the layout pass 4 wants: K[kk][pos] = 0.5/(108*108) * DFT2(kernel)[u(pos)][v(kk)],
-// computed separably straight from the taps (the kernel is tiny; one CTA).
+// Kernel spectrum in the layout pass 4 wants: K[pos][kk] = 0.5/(108*108) * DFT2(kernel)[u(kk)][v(pos)]
+// (u = vertical frequency of half-spectrum column kk, v = horizontal frequency at scrambled
+// position pos), computed separably straight from the taps (the kernel is tiny; one CTA).
 __global__ void __launch_bounds__(512, 1) kspec_kernel(const double* __restrict__ ker, int hk, int wk,
                                                        const cplx* __restrict__ tw, cplx* __restrict__ out) {
-  cplx* T1 = reinterpret_cast<cplx*>(b2c_smem_t108);  // [hke][NK]
+  cplx* T1 = reinterpret_cast<cplx*>(b2c_smem_t108);  // [wke][NK]
   const int hke = min(hk, P), wke = min(wk, P);
-  for (int idx = threadIdx.x; idx < hke * NK; idx += blockDim.x) {
-    const int i = idx / NK, kk = idx - i * NK;
-    const int v = freq_of_pos(rep_of(kk));
+  for (int idx = threadIdx.x; idx < wke * NK; idx += blockDim.x) {
+    const int b = idx / NK, kk = idx - b * NK;
+    const int u = freq_of_pos(rep_of(kk));
     cplx acc = make_double2(0.0, 0.0);
-    for (int c = 0; c < wke; ++c) {
+    for (int a = 0; a < hke; ++a) {
       double tap = 0.0;   // taps congruent modulo the period add up (convolution_fftw.h:185-187)
-      for (int ii = i; ii < hk; ii += P)
-        for (int cc = c; cc < wk; cc += P) tap += ker[(size_t)ii * wk + cc];
-      const cplx w = tw[(v * c) % P];
+      for (int aa = a; aa < hk; aa += P)
+        for (int bb = b; bb < wk; bb += P) tap += ker[(size_t)aa * wk + bb];
+      const cplx w = tw[(u * a) % P];
       acc.x = fma(tap, w.x, acc.x);
       acc.y = fma(tap, w.y, acc.y);
     }
@@ -299,13 +304,13 @@ __global__ void __launch_bounds__(512, 1) kspec_kernel(const double* __restrict_
   }
   __syncthreads();
   const double scale = 0.5 / ((double)P * (double)P);
-  for (int idx = threadIdx.x; idx < NK * P; idx += blockDim.x) {
-    const int kk = idx / P, pos = idx - kk * P;
-    const int u = freq_of_pos(pos);
+  for (int idx = threadIdx.x; idx < P * NK; idx += blockDim.x) {
+    const int pos = idx / NK, kk = idx - pos * NK;
+    const int v = freq_of_pos(pos);
     cplx acc = make_double2(0.0, 0.0);
-    for (int i = 0; i < hke; ++i) {
-      const cplx a = T1[i * NK + kk];
-      const cplx w = tw[(u * i) % P];
+    for (int b = 0; b < wke; ++b) {
+      const cplx a = T1[b * NK + kk];
+      const cplx w = tw[(v * b) % P];
       acc.x += a.x * w.x - a.y * w.y;
       acc.y += a.x * w.y + a.y * w.x;
     }
@@ -319,7 +324,7 @@ size_t tuned108_smem_bytes() { return sizeof(cplx) * t108::HALF * t108::LD; }
 size_t tuned108_kspec_bytes() { return sizeof(cplx) * t108::NK * t108::P; }
 
 cudaError_t launch_tuned108_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st) {
-  const size_t smem = sizeof(cplx) * (size_t)(hk < t108::P ? hk : t108::P) * t108::NK;
+  const size_t smem = sizeof(cplx) * (size_t)(wk < t108::P ? wk : t108::P) * t108::NK;
   cudaFuncSetAttribute(t108::kspec_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   t108::kspec_kernel<<<1, 512, smem, st>>>(d_ker, hk, wk, tw, out);
   return cudaGetLastError();
