@@ -334,6 +334,14 @@ void free_pipe(b2c_plan* p) {
 
 }  // namespace
 
+// Lets other translation units of the library report through b2c_last_error().
+namespace b2c {
+int set_last_error(int code, const char* text) {
+  g_err = text;
+  return code;
+}
+}  // namespace b2c
+
 extern "C" {
 
 const char* b2c_last_error(void) { return g_err.c_str(); }

@@ -78,6 +78,25 @@ int b2c_convolve_batch_host(b2c_plan* plan, const double* src, const double* ker
 int b2c_convolve_batch_device(b2c_plan* plan, const double* d_src, const double* d_kernel,
                               int kernel_is_shared, double* d_dst, long n_images, void* cuda_stream);
 
+/* No counterpart in the reference.  Batched shared-kernel convolution with DEVICE buffers that
+ * calls no cudaMalloc / cudaFree / allocating routine at all -- for callers that cannot allocate
+ * GPU memory when they convolve: plug-ins inside an application whose memory pool already owns the
+ * whole GPU, latency-critical loops that cannot take cudaMalloc's device-wide synchronisation, code
+ * under a fixed memory budget.  Its scratch (kernel spectrum + root table of the tuned 108 x 108
+ * kernel) is one file-scope device array of 96 960 bytes that every GPU using the library holds
+ * until exit; the caller passes only inputs and outputs.
+ * Limit: both alias-safe periods must be <= 108 (e.g. LINEAR_SAME needs h_src + h_kernel/2 <= 108,
+ * LINEAR_FULL h_src + h_kernel - 1 <= 108, same for widths; CIRCULAR_SAME only for 108 x 108
+ * sources); larger problems return B2C_ESIZE with a message naming the required periods.
+ * The first call on a device does a one-off set-up (address look-up + blocking upload of the root
+ * table): make it before any stream capture on that device.  All calls share the array, which
+ * keeps the previous call's spectrum; each call rewrites it before use, so nothing needs clearing,
+ * but calls whose GPU work overlaps race -- serialise them (one stream, or events).
+ * Layouts as b2c_convolve_batch_device with kernel_is_shared = 1; asynchronous on `cuda_stream`. */
+int b2c_convolve_batch_device_static(int mode, int h_src, int w_src, int h_kernel, int w_kernel,
+                                     const double* d_src, const double* d_kernel, double* d_dst,
+                                     long n_images, void* cuda_stream);
+
 /* The reference planner, restated for callers that want its sizes (factorize.h:92-104 with
  * FFTW_FACTORS of convolution_fftw.h:15, including the "no multiple of 4" quirk of :74). */
 int b2c_find_closest_factor(int n);
