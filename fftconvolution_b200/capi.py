@@ -35,7 +35,8 @@ class B2CError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(_HERE, "lib", "libb2conv.so")
+    # B2C_LIB_PATH: A/B-test another build of the same library (tools/quick_bench.py); never a fallback
+    return os.environ.get("B2C_LIB_PATH") or os.path.join(_HERE, "lib", "libb2conv.so")
 
 
 _lib = None

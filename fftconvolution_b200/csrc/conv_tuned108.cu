@@ -32,6 +32,8 @@ constexpr int P = 108;
 constexpr int HALF = 54;
 constexpr int LD = 115;          // odd stride (bank groups), chosen with tools/bank_sim_t108.py
 constexpr int NK = 55;          // half-spectrum columns
+constexpr int KLD = 56;         // kernel-spectrum row pitch (896 B = 7 cache lines)
+constexpr int BPAD = 56;        // radix-9 passes index 56 lines per block so block changes fall on quarter-warp edges
 constexpr int THREADS = 256;
 constexpr int A_LINES = 28;     // radix-12 passes: 28 lines x 9 butterflies = 252 active threads per round
 
@@ -40,7 +42,7 @@ struct Params {
   const double* src;
   double* dst;
   long n_images;
-  const cplx* kspec;  // [P][NK]: (scrambled horizontal position, half-spectrum vertical frequency kk)
+  const cplx* kspec;  // [P][KLD]: (scrambled horizontal position, half-spectrum vertical frequency kk)
   const cplx* tw;     // exp(-2 pi i k / 108)
 };
 
@@ -153,8 +155,9 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
 
     // ---- pass 2: vertical forward radix-9 (task = block pb of line `line`)
 #pragma unroll 1
-    for (int task = t; task < 12 * HALF; task += THREADS) {
-      const int pb = task / HALF, line = task - pb * HALF;
+    for (int task = t; task < 12 * BPAD; task += THREADS) {
+      const int pb = task / BPAD, line = task - pb * BPAD;
+      if (line >= HALF) continue;
       cplx* z = Z + line * LD + 9 * pb;
       cplx v[9];
 #pragma unroll
@@ -194,17 +197,18 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
 
     // ---- pass 4: horizontal radix-9 forward, spectrum product, radix-9 backward
 #pragma unroll 1
-    for (int task = t; task < 12 * NK; task += THREADS) {
-      const int pb = task / NK, kk = task - pb * NK;
+    for (int task = t; task < 12 * BPAD; task += THREADS) {
+      const int pb = task / BPAD, kk = task - pb * BPAD;
+      if (kk >= NK) continue;
       const int col = pb < 6 ? rep_of(kk) : par_of(kk);
       cplx* z = Z + (9 * (pb < 6 ? pb : pb - 6)) * LD + col;
-      const cplx* __restrict__ ks = p.kspec + (9 * pb) * NK + kk;
+      const cplx* __restrict__ ks = p.kspec + (9 * pb) * KLD + kk;
       cplx v[9];
 #pragma unroll
       for (int s = 0; s < 9; ++s) v[s] = z[s * LD];
       bfly9(v);
 #pragma unroll
-      for (int s = 0; s < 9; ++s) v[s] = cswap(cmul(v[s], __ldg(ks + s * NK)));   // product, swapped for the inverse
+      for (int s = 0; s < 9; ++s) v[s] = cswap(cmul(v[s], __ldg(ks + s * KLD)));   // product, swapped for the inverse
       bfly9(v);
 #pragma unroll
       for (int s = 0; s < 9; ++s) z[s * LD] = cswap(v[s]);
@@ -240,8 +244,9 @@ __global__ void __launch_bounds__(THREADS, 2) conv_kernel(const __grid_constant_
 
     // ---- pass 6: vertical backward radix-9
 #pragma unroll 1
-    for (int task = t; task < 12 * HALF; task += THREADS) {
-      const int pb = task / HALF, line = task - pb * HALF;
+    for (int task = t; task < 12 * BPAD; task += THREADS) {
+      const int pb = task / BPAD, line = task - pb * BPAD;
+      if (line >= HALF) continue;
       cplx* z = Z + line * LD + 9 * pb;
       cplx v[9];
 #pragma unroll
@@ -314,14 +319,14 @@ __global__ void __launch_bounds__(512, 1) kspec_kernel(const double* __restrict_
       acc.x += a.x * w.x - a.y * w.y;
       acc.y += a.x * w.y + a.y * w.x;
     }
-    out[idx] = make_double2(acc.x * scale, acc.y * scale);
+    out[pos * KLD + kk] = make_double2(acc.x * scale, acc.y * scale);
   }
 }
 
 }  // namespace t108
 
 size_t tuned108_smem_bytes() { return sizeof(cplx) * t108::HALF * t108::LD; }
-size_t tuned108_kspec_bytes() { return sizeof(cplx) * t108::NK * t108::P; }
+size_t tuned108_kspec_bytes() { return sizeof(cplx) * t108::KLD * t108::P; }
 
 cudaError_t launch_tuned108_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st) {
   const size_t smem = sizeof(cplx) * (size_t)(wk < t108::P ? wk : t108::P) * t108::NK;

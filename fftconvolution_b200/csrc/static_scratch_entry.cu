@@ -11,7 +11,7 @@
 //
 // What it does instead: the scratch of the tuned 108 x 108 kernel (conv_tuned108.cu) -- the
 // kernel's spectrum and the table of 108th roots of unity -- lives in ONE file-scope device array
-// of 96 960 bytes that every GPU loading this library carries until the process exits.  The caller
+// of 98 496 bytes that every GPU loading this library carries until the process exits.  The caller
 // passes only its own input and output buffers.  Any problem whose alias-safe periods fit in 108 on
 // both axes is run at the fixed period 108 x 108; anything larger is refused (B2C_ESIZE).
 //
@@ -48,10 +48,10 @@ int set_last_error(int code, const char* text);
 namespace {
 
 constexpr int kPeriod = 108;                                   // the only period this entry point runs
-constexpr size_t kSpecBytes = sizeof(double2) * 108 * 55;      // kernel spectrum, half spectrum of one axis
-constexpr size_t kRootsOffset = 95232;                         // next multiple of 256 after kSpecBytes
+constexpr size_t kSpecBytes = sizeof(double2) * 108 * 56;      // kernel spectrum: 108 positions x 55 frequencies, row pitch 56
+constexpr size_t kRootsOffset = 96768;                         // = kSpecBytes, a multiple of 256
 constexpr size_t kRootsBytes = sizeof(double2) * kPeriod;
-constexpr size_t kScratchBytes = kRootsOffset + kRootsBytes;   // 96 960 bytes per GPU, for the life of the process
+constexpr size_t kScratchBytes = kRootsOffset + kRootsBytes;   // 98 496 bytes per GPU, for the life of the process
 static_assert(kSpecBytes <= kRootsOffset, "layout");
 
 // The scratch itself.  In host code this name is only a handle for cudaGetSymbolAddress -- it is

@@ -83,7 +83,7 @@ int b2c_convolve_batch_device(b2c_plan* plan, const double* d_src, const double*
  * GPU memory when they convolve: plug-ins inside an application whose memory pool already owns the
  * whole GPU, latency-critical loops that cannot take cudaMalloc's device-wide synchronisation, code
  * under a fixed memory budget.  Its scratch (kernel spectrum + root table of the tuned 108 x 108
- * kernel) is one file-scope device array of 96 960 bytes that every GPU using the library holds
+ * kernel) is one file-scope device array of 98 496 bytes that every GPU using the library holds
  * until exit; the caller passes only inputs and outputs.
  * Limit: both alias-safe periods must be <= 108 (e.g. LINEAR_SAME needs h_src + h_kernel/2 <= 108,
  * LINEAR_FULL h_src + h_kernel - 1 <= 108, same for widths; CIRCULAR_SAME only for 108 x 108
