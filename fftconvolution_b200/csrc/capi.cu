@@ -27,7 +27,7 @@ int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 // conv_direct.cu
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
-int occupancy_direct(size_t smem);
+int occupancy_direct(int hk, size_t smem);
 // conv_tuned108.cu
 size_t tuned108_smem_bytes();
 size_t tuned108_kspec_bytes();
@@ -163,7 +163,10 @@ struct b2c_plan {
 
 namespace {
 
-size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (size_t)pl.w.P; }
+// leading dimension of the generic work buffer: odd, so that a walk down a column (stride ld)
+// touches all eight 16-byte bank groups
+int work_ld(const Plan2D& pl) { return pl.w.P | 1; }
+size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (size_t)work_ld(pl); }
 
 // Cost-model crossover between the direct kernel and the FFT chain (refined by measurement,
 // see DESIGN.md): FP64 instruction estimates per image for both.
@@ -236,7 +239,7 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
   q.hd = pl.h.n_dst; q.wd = pl.w.n_dst;
   q.off_h = pl.h.off; q.off_w = pl.w.off; q.fold_h = pl.h.fold; q.fold_w = pl.w.fold;
   q.lin_h = pl.h.lin; q.lin_w = pl.w.lin; q.kwrap_h = pl.h.kwrap; q.kwrap_w = pl.w.kwrap;
-  q.ld = pl.w.P;
+  q.ld = work_ld(pl);
   fill_axis(q.ah, pl.h, p->th);
   fill_axis(q.aw, pl.w, p->tw);
   q.scale = 1.0 / ((double)pl.h.P * (double)pl.w.P);
@@ -300,7 +303,7 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   q.tiles_per_image = (q.hd + tile - 1) / tile;
   const size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw);
   q.sp_w = spw;
-  int occ = occupancy_direct(smem);
+  int occ = occupancy_direct(q.hk, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);
@@ -382,6 +385,11 @@ int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kerne
   if (!make_plan(mode, h_src, w_src, h_kernel, w_kernel, p->pl)) {
     delete p;
     return fail(B2C_EINVAL, "b2c_plan_create: planning failed");
+  }
+  if (!p->pl.empty && (long)p->pl.h.P * (long)work_ld(p->pl) >= (1L << 24)) {
+    const int ph = p->pl.h.P, pw = p->pl.w.P;
+    delete p;
+    return fail(B2C_ESIZE, "b2c_plan_create: transform of %d x %d points exceeds the engine's work-buffer index range", ph, pw);
   }
   *plan = p;
   return 0;

@@ -1,28 +1,39 @@
 // Direct (nested-loop) convolution kernel for small kernels, where the reference itself finds
 // loops faster than the FFT (README.md:31,47; Convolution/src/convolution_std.h:86-199 is the
-// CPU form).  One CTA stages a row tile of the source (zero- or wrap-padded halo) plus the
-// flipped kernel in shared memory; every thread produces TJ=8 adjacent outputs with a sliding
-// register window, so each shared-memory word feeds 8 FP64 FMAs.
+// CPU form).
+//
+// One CTA stages a row tile of the source (zero- or wrap-padded halo) and the flipped kernel in
+// shared memory.  A thread owns ONE output column and TI = 8 consecutive output rows; lanes of a
+// warp walk adjacent columns, so shared-memory reads are conflict-free 64-bit accesses and global
+// stores are coalesced.  For every kernel column the thread loads a vertical window of
+// TI + HK - 1 source values into registers and performs TI * HK FMAs on it; HK (the kernel height)
+// is a template parameter so that the window lives in registers.  Kernels taller than
+// kMaxDirectHK use the general variant (one load per FMA), which only matters for forced-path
+// tests: the planner never picks the direct path there.
 #include "conv_params.h"
 
 namespace b2c {
 
 extern __shared__ __align__(16) unsigned char b2c_smem_direct[];
 
-constexpr int TJ = 8;
+constexpr int TI = 8;
+constexpr int kMaxDirectHK = 16;
+constexpr int kDirectThreads = 256;
 
 __device__ __forceinline__ int wrap_index(int x, int m) {
   x %= m;
   return x < 0 ? x + m : x;
 }
 
-__global__ void __launch_bounds__(256, 2) direct_kernel(const __grid_constant__ DirectParams p) {
-  double* kflip = reinterpret_cast<double*>(b2c_smem_direct);
-  const int wk_pad = (p.wk + TJ - 1) / TJ * TJ;
-  double* S = kflip + (size_t)p.hk * wk_pad;
-  const int sp_w = p.sp_w;
+// HK > 0: compile-time kernel height; HK == 0: run-time height (general variant).
+template <int HK>
+__global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_constant__ DirectParams p) {
+  double* kflip = reinterpret_cast<double*>(b2c_smem_direct);   // [wk][hk_pad]: column-major, flipped
+  const int hk = HK > 0 ? HK : p.hk;
+  const int hk_pad = (hk + 1) & ~1;
+  double* S = kflip + (size_t)p.wk * hk_pad;
+  const int pitch = p.sp_w;
   const size_t src_sz = (size_t)p.hs * p.ws, ker_sz = (size_t)p.hk * p.wk, dst_sz = (size_t)p.hd * p.wd;
-  const int groups = (p.wd + TJ - 1) / TJ;
   const long total = p.n_images * p.tiles_per_image;
   bool kernel_loaded = false;
 
@@ -34,87 +45,124 @@ __global__ void __launch_bounds__(256, 2) direct_kernel(const __grid_constant__ 
     __syncthreads();  // previous iteration's readers are done
     if (!(p.kernel_is_shared && kernel_loaded)) {
       const double* k = p.ker + (p.kernel_is_shared ? 0 : (size_t)img * ker_sz);
-      for (int idx = threadIdx.x; idx < p.hk * wk_pad; idx += blockDim.x) {
-        const int r = idx / wk_pad, c = idx - r * wk_pad;
-        kflip[idx] = c < p.wk ? __ldg(&k[(size_t)(p.hk - 1 - r) * p.wk + (p.wk - 1 - c)]) : 0.0;
+      for (int idx = threadIdx.x; idx < p.wk * hk_pad; idx += kDirectThreads) {
+        const int c = idx / hk_pad, r = idx - c * hk_pad;
+        kflip[idx] = r < hk ? __ldg(&k[(size_t)(hk - 1 - r) * p.wk + (p.wk - 1 - c)]) : 0.0;
       }
       kernel_loaded = true;
     }
-    // stage source rows i0+off_h-(hk-1) ... with halo
+    // stage source rows [i0 + off_h - (hk-1), ...) with halo.  Eight independent global loads are in
+    // flight per thread before the first shared store (the staging loop is latency-, not bandwidth-bound).
     const double* a = p.src + (size_t)img * src_sz;
-    const int rows = th + p.hk - 1;
-    for (int idx = threadIdx.x; idx < rows * sp_w; idx += blockDim.x) {
-      const int u = idx / sp_w, v = idx - u * sp_w;
-      int sr = i0 + u + p.off_h - (p.hk - 1);
-      int sc = v + p.off_w - (p.wk - 1);
-      double val = 0.0;
-      if (v < p.wd + p.wk - 1) {
-        if (p.wrap_h) sr = wrap_index(sr, p.wrap_h);
-        if (p.wrap_w) sc = wrap_index(sc, p.wrap_w);
-        if (sr >= 0 && sr < p.hs && sc >= 0 && sc < p.ws) val = __ldg(&a[(size_t)sr * p.ws + sc]);
+    const int rows = th + hk - 1;
+    const int cols = p.wd + p.wk - 1;
+    const int nelem = rows * pitch;
+    const float inv_pitch = 1.0f / (float)pitch;
+    constexpr int SU = 8;
+    for (int base = threadIdx.x; base < nelem; base += SU * kDirectThreads) {
+      double vals[SU];
+#pragma unroll
+      for (int k = 0; k < SU; ++k) {
+        const int idx = base + k * kDirectThreads;
+        double val = 0.0;
+        if (idx < nelem) {
+          const int u = fast_div(idx, pitch, inv_pitch), v = idx - u * pitch;
+          int sr = i0 + u + p.off_h - (hk - 1);
+          int sc = v + p.off_w - (p.wk - 1);
+          if (p.wrap_h) sr = wrap_index(sr, p.wrap_h);
+          if (p.wrap_w) sc = wrap_index(sc, p.wrap_w);
+          if (v < cols && sr >= 0 && sr < p.hs && sc >= 0 && sc < p.ws) val = __ldg(a + (size_t)sr * p.ws + sc);
+        }
+        vals[k] = val;
       }
-      S[idx] = val;
+#pragma unroll
+      for (int k = 0; k < SU; ++k) {
+        const int idx = base + k * kDirectThreads;
+        if (idx < nelem) S[idx] = vals[k];
+      }
     }
     __syncthreads();
     double* d = p.dst + (size_t)img * dst_sz;
-    for (int task = threadIdx.x; task < th * groups; task += blockDim.x) {
-      const int g = task / th, i = task - g * th;   // adjacent lanes -> adjacent rows (bank-conflict free)
-      const int j0 = g * TJ;
-      double acc[TJ];
+    const int blocks = (th + TI - 1) / TI;
+    for (int task = threadIdx.x; task < blocks * p.wd; task += kDirectThreads) {
+      const int b = task / p.wd, j = task - b * p.wd;   // adjacent lanes -> adjacent columns
+      const int r0 = b * TI;
+      double acc[TI];
 #pragma unroll
-      for (int t = 0; t < TJ; ++t) acc[t] = 0.0;
-      for (int kr = 0; kr < p.hk; ++kr) {
-        const double* row = S + (size_t)(i + kr) * sp_w + j0;
-        const double* kv = kflip + (size_t)kr * wk_pad;
-        double w[2 * TJ];
+      for (int t = 0; t < TI; ++t) acc[t] = 0.0;
+      const double* col = S + (size_t)r0 * pitch + j;
+      if (HK > 0) {
+        // rows beyond the tile's halo are never read for outputs that exist: clamp the window
+        const int last = rows - 1 - r0;   // highest valid window index
+        for (int kc = 0; kc < p.wk; ++kc) {
+          double w[TI + (HK > 0 ? HK : 1) - 1];
 #pragma unroll
-        for (int t = 0; t < TJ; t += 2) {
-          double2 x = *reinterpret_cast<const double2*>(row + t);
-          w[t] = x.x; w[t + 1] = x.y;
+          for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[(size_t)min(u, last) * pitch + kc];
+          const double* kv = kflip + kc * hk_pad;
+#pragma unroll
+          for (int kr = 0; kr < HK; ++kr) {
+            const double kk = kv[kr];
+#pragma unroll
+            for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
+          }
         }
-        for (int l0 = 0; l0 < wk_pad; l0 += TJ) {
+      } else {
+        const int nt = min(TI, th - r0);
+        for (int kc = 0; kc < p.wk; ++kc) {
+          const double* kv = kflip + kc * hk_pad;
+          for (int kr = 0; kr < hk; ++kr) {
+            const double kk = kv[kr];
 #pragma unroll
-          for (int t = 0; t < TJ; t += 2) {
-            double2 x = *reinterpret_cast<const double2*>(row + l0 + TJ + t);
-            w[TJ + t] = x.x; w[TJ + t + 1] = x.y;
+            for (int t = 0; t < TI; ++t)
+              if (t < nt) acc[t] = fma(kk, col[(size_t)(t + kr) * pitch + kc], acc[t]);
           }
-#pragma unroll
-          for (int dl = 0; dl < TJ; ++dl) {
-            const double kk = kv[l0 + dl];
-#pragma unroll
-            for (int t = 0; t < TJ; ++t) acc[t] = fma(kk, w[dl + t], acc[t]);
-          }
-#pragma unroll
-          for (int t = 0; t < TJ; ++t) w[t] = w[TJ + t];
         }
       }
-      double* o = d + (size_t)(i0 + i) * p.wd + j0;
+      double* o = d + (size_t)(i0 + r0) * p.wd + j;
 #pragma unroll
-      for (int t = 0; t < TJ; ++t)
-        if (j0 + t < p.wd) o[t] = acc[t];
+      for (int t = 0; t < TI; ++t)
+        if (r0 + t < th) o[(size_t)t * p.wd] = acc[t];
     }
   }
 }
 
-// Shared memory the direct kernel needs for a given row tile; sp_w is returned through *sp_w_out.
+// Shared memory the direct kernel needs for a given row tile; the staged row pitch is returned
+// through *sp_w_out.
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out) {
-  const int wk_pad = (wk + TJ - 1) / TJ * TJ;
-  int sp_w = (wd + TJ - 1) / TJ * TJ + wk_pad + TJ;
-  while (sp_w % 16 != 2) ++sp_w;  // row stride == 4 (mod 32) words: 8 lanes x 128-bit hit 32 banks
-  if (sp_w_out) *sp_w_out = sp_w;
-  return sizeof(double) * ((size_t)hk * wk_pad + (size_t)(tile_h + hk - 1) * sp_w);
+  const int hk_pad = (hk + 1) & ~1;
+  int pitch = wd + wk - 1;
+  pitch = (pitch + 1) & ~1;
+  if (sp_w_out) *sp_w_out = pitch;
+  return sizeof(double) * ((size_t)wk * hk_pad + (size_t)(tile_h + hk - 1) * pitch);
+}
+
+typedef void (*direct_fn)(const DirectParams);
+
+template <int HK>
+static direct_fn pick() { return direct_kernel<HK>; }
+
+static direct_fn direct_variant(int hk) {
+  switch (hk) {
+    case 1: return pick<1>();   case 2: return pick<2>();   case 3: return pick<3>();   case 4: return pick<4>();
+    case 5: return pick<5>();   case 6: return pick<6>();   case 7: return pick<7>();   case 8: return pick<8>();
+    case 9: return pick<9>();   case 10: return pick<10>(); case 11: return pick<11>(); case 12: return pick<12>();
+    case 13: return pick<13>(); case 14: return pick<14>(); case 15: return pick<15>(); case 16: return pick<16>();
+  }
+  return pick<0>();
 }
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
-  cudaFuncSetAttribute(direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  direct_kernel<<<grid, 256, smem, st>>>(p);
+  direct_fn fn = direct_variant(p.hk);
+  cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  fn<<<grid, kDirectThreads, smem, st>>>(p);
   return cudaGetLastError();
 }
 
-int occupancy_direct(size_t smem) {
+int occupancy_direct(int hk, size_t smem) {
   int n = 0;
-  cudaFuncSetAttribute(direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, direct_kernel, 256, smem);
+  direct_fn fn = direct_variant(hk);
+  cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
   return n;
 }
 

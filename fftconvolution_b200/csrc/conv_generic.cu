@@ -39,9 +39,10 @@ template <bool SMEM>
 __global__ void __launch_bounds__(512, 1) kspec_kernel(const __grid_constant__ ConvParams p) {
   cplx* W = work_buffer<SMEM>(p);
   const int Ph = p.ah.P, Pw = p.aw.P, ld = p.ld;
+  const float inv_ld = 1.0f / (float)ld, inv_pw = 1.0f / (float)Pw, inv_wd = 1.0f / (float)(p.wd > 0 ? p.wd : 1);
   const int hke = min(p.hk, p.kwrap_h), wke = min(p.wk, p.kwrap_w);
   for (int idx = threadIdx.x; idx < Ph * ld; idx += blockDim.x) {
-    const int r = idx / ld, c = idx - r * ld;
+    const int r = fast_div(idx, ld, inv_ld), c = idx - r * ld;
     double v = 0.0;
     if (r < hke && c < wke) v = wrapped_tap(p, p.ker, r, c);
     W[idx] = make_double2(v, 0.0);
@@ -50,7 +51,7 @@ __global__ void __launch_bounds__(512, 1) kspec_kernel(const __grid_constant__ C
   fft_forward(p.aw, W, 1, ld, hke, false);
   fft_forward(p.ah, W, ld, 1, Pw, true);
   for (int idx = threadIdx.x; idx < Ph * Pw; idx += blockDim.x) {
-    const int r = idx / Pw, c = idx - r * Pw;
+    const int r = fast_div(idx, Pw, inv_pw), c = idx - r * Pw;
     cplx v = W[r * ld + c];
     p.kspec[idx] = make_double2(v.x * p.scale, v.y * p.scale);
   }
@@ -77,6 +78,7 @@ template <bool SMEM>
 __global__ void __launch_bounds__(512, 1) conv_shared_kernel(const __grid_constant__ ConvParams p) {
   cplx* W = work_buffer<SMEM>(p);
   const int Ph = p.ah.P, Pw = p.aw.P, ld = p.ld;
+  const float inv_ld = 1.0f / (float)ld, inv_pw = 1.0f / (float)Pw, inv_wd = 1.0f / (float)(p.wd > 0 ? p.wd : 1);
   const long npairs = (p.n_images + 1) / 2;
   const size_t src_sz = (size_t)p.hs * p.ws, dst_sz = (size_t)p.hd * p.wd;
   const int row0 = p.fold_h ? 0 : p.off_h;
@@ -87,20 +89,30 @@ __global__ void __launch_bounds__(512, 1) conv_shared_kernel(const __grid_consta
     const bool has_b = 2 * pair + 1 < p.n_images;
     const double* b = a + src_sz;
     // zero-pad on load (convolution_fftw.h:174-183; the source never wraps because P >= n_src)
-    for (int idx = threadIdx.x; idx < Ph * ld; idx += blockDim.x) {
-      const int r = idx / ld, c = idx - r * ld;
-      cplx v = make_double2(0.0, 0.0);
-      if (r < p.hs && c < p.ws) {
-        v.x = __ldg(&a[r * p.ws + c]);
-        if (has_b) v.y = __ldg(&b[r * p.ws + c]);
+    // (four elements per thread per trip: eight independent global loads in flight before the stores)
+    for (int base = threadIdx.x; base < Ph * ld; base += 4 * blockDim.x) {
+      cplx v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int idx = base + k * blockDim.x;
+        const int r = fast_div(idx, ld, inv_ld), c = idx - r * ld;
+        v[k] = make_double2(0.0, 0.0);
+        if (idx < Ph * ld && r < p.hs && c < p.ws) {
+          v[k].x = __ldg(&a[r * p.ws + c]);
+          if (has_b) v[k].y = __ldg(&b[r * p.ws + c]);
+        }
       }
-      W[idx] = v;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int idx = base + k * blockDim.x;
+        if (idx < Ph * ld) W[idx] = v[k];
+      }
     }
     __syncthreads();
     fft_forward(p.aw, W, 1, ld, p.hs, false);   // rows that hold data
     fft_forward(p.ah, W, ld, 1, Pw, true);      // every column
     for (int idx = threadIdx.x; idx < Ph * Pw; idx += blockDim.x) {   // convolution_fftw.h:195-204
-      const int r = idx / Pw, c = idx - r * Pw;
+      const int r = fast_div(idx, Pw, inv_pw), c = idx - r * Pw;
       W[r * ld + c] = cmul(W[r * ld + c], __ldg(&p.kspec[idx]));
     }
     __syncthreads();
@@ -110,7 +122,7 @@ __global__ void __launch_bounds__(512, 1) conv_shared_kernel(const __grid_consta
     double* da = p.dst + (size_t)(2 * pair) * dst_sz;
     double* db = da + dst_sz;
     for (int idx = threadIdx.x; idx < p.hd * p.wd; idx += blockDim.x) {
-      const int i = idx / p.wd, j = idx - i * p.wd;
+      const int i = fast_div(idx, p.wd, inv_wd), j = idx - i * p.wd;
       cplx v = folded_value(p, W, i, j);
       da[idx] = v.x;
       if (has_b) db[idx] = v.y;
@@ -125,6 +137,7 @@ template <bool SMEM>
 __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_constant__ ConvParams p) {
   cplx* W = work_buffer<SMEM>(p);
   const int Ph = p.ah.P, Pw = p.aw.P, ld = p.ld;
+  const float inv_ld = 1.0f / (float)ld, inv_pw = 1.0f / (float)Pw, inv_wd = 1.0f / (float)(p.wd > 0 ? p.wd : 1);
   const size_t src_sz = (size_t)p.hs * p.ws, ker_sz = (size_t)p.hk * p.wk, dst_sz = (size_t)p.hd * p.wd;
   const int hke = min(p.hk, p.kwrap_h), wke = min(p.wk, p.kwrap_w);
   const int rows_in = max(p.hs, hke);
@@ -135,12 +148,23 @@ __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_cons
   for (long img = blockIdx.x; img < p.n_images; img += gridDim.x) {
     const double* a = p.src + (size_t)img * src_sz;
     const double* k = p.ker + (size_t)img * ker_sz;
-    for (int idx = threadIdx.x; idx < Ph * ld; idx += blockDim.x) {
-      const int r = idx / ld, c = idx - r * ld;
-      cplx v = make_double2(0.0, 0.0);
-      if (r < p.hs && c < p.ws) v.x = __ldg(&a[r * p.ws + c]);
-      if (r < hke && c < wke) v.y = plain_kernel ? __ldg(&k[r * p.wk + c]) : wrapped_tap(p, k, r, c);
-      W[idx] = v;
+    for (int base = threadIdx.x; base < Ph * ld; base += 4 * blockDim.x) {
+      cplx v[4];
+#pragma unroll
+      for (int kq = 0; kq < 4; ++kq) {
+        const int idx = base + kq * blockDim.x;
+        const int r = fast_div(idx, ld, inv_ld), c = idx - r * ld;
+        v[kq] = make_double2(0.0, 0.0);
+        if (idx < Ph * ld) {
+          if (r < p.hs && c < p.ws) v[kq].x = __ldg(&a[r * p.ws + c]);
+          if (r < hke && c < wke) v[kq].y = plain_kernel ? __ldg(&k[r * p.wk + c]) : wrapped_tap(p, k, r, c);
+        }
+      }
+#pragma unroll
+      for (int kq = 0; kq < 4; ++kq) {
+        const int idx = base + kq * blockDim.x;
+        if (idx < Ph * ld) W[idx] = v[kq];
+      }
     }
     __syncthreads();
     fft_forward(p.aw, W, 1, ld, rows_in, false);
@@ -149,7 +173,7 @@ __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_cons
     // => S*K = (Z(w)^2 - conj(Z(-w))^2) / (4i).  The (-w) partner sits at (neg_h[r], neg_w[c]).
     const double q = 0.25 * p.scale;
     for (int idx = threadIdx.x; idx < Ph * Pw; idx += blockDim.x) {
-      const int r = idx / Pw, c = idx - r * Pw;
+      const int r = fast_div(idx, Pw, inv_pw), c = idx - r * Pw;
       const int pr = __ldg(&p.ah.neg[r]), pc = __ldg(&p.aw.neg[c]);
       const int pidx = pr * Pw + pc;
       if (pidx < idx) continue;  // the partner's thread writes both
@@ -165,7 +189,7 @@ __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_cons
     fft_backward(p.aw, W + (size_t)row0 * ld, 1, ld, nrows, false);
     double* d = p.dst + (size_t)img * dst_sz;
     for (int idx = threadIdx.x; idx < p.hd * p.wd; idx += blockDim.x) {
-      const int i = idx / p.wd, j = idx - i * p.wd;
+      const int i = fast_div(idx, p.wd, inv_wd), j = idx - i * p.wd;
       d[idx] = folded_value(p, W, i, j).x;
     }
     __syncthreads();
