@@ -136,6 +136,23 @@ def time_cpu_reference(n_sample, threads, reps=1):
     return n_sample / best, kind, best
 
 
+def time_cpu_scipy_port(n_sample, threads):
+    """A modern-CPU restatement of convolution_fftw.h:169-284 on scipy.fft (pocketfft, SIMD, `threads`
+    workers) at the reference's own period (find_closest_factor -> 110 x 110).  Extra information only."""
+    import numpy as np
+    import scipy.fft as sfft
+    import _oracle
+    P, off = 110, HK // 2
+    src = _oracle.splitmix_uniform(SEED, 0, n_sample * H * W).reshape(n_sample, H, W)
+    ker = np.random.default_rng(SEED).random((HK, WK))
+    t0 = time.perf_counter()
+    ks = sfft.rfft2(ker, s=(P, P))
+    out = sfft.irfft2(sfft.rfft2(src, s=(P, P), workers=threads) * ks, s=(P, P), workers=threads)[:, off:off + H, off:off + W]
+    out = np.ascontiguousarray(out)
+    dt = time.perf_counter() - t0
+    return n_sample / dt, dt
+
+
 def cpu_sample_size(threads, target_s):
     """Calibrate a bounded sample (about target_s seconds of CPU work on `threads` threads)."""
     rate, _, _ = time_cpu_reference(4 * threads, threads)
@@ -298,6 +315,13 @@ def run_b2c_arm(args):
                             n_sample, BATCH,
                             "unmodified over stand-in FFT (no libfftw3 on box)" if kind == "reference" else "restated (oracle port)",
                             cores, dt)}
+        try:
+            n2 = 4096
+            r2, d2 = time_cpu_scipy_port(n2, cores)
+            cpu_baseline["scipy_pocketfft_port"] = {"value": r2, "unit": UNIT, "cores": cores,
+                                                    "sample": "%d images, rfft2/irfft2 at period 110 (%.2f s)" % (n2, d2)}
+        except Exception as ex:
+            cpu_baseline["scipy_pocketfft_port"] = {"error": str(ex)[:100]}
 
     if rank == 0:
         line = {

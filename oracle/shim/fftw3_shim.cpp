@@ -42,13 +42,25 @@ fftw_plan fftw_plan_dft_c2r_2d(int n0, int n1, fftw_complex* in, double* out, un
 void fftw_execute(const fftw_plan p) {
   const int h = p->h, w = p->w, wh = p->wh;
   if (h <= 0 || w <= 0) return;
-  std::complex<double>* a = p->a.data();
-  std::complex<double>* b = p->b.data();
+  typedef std::complex<double> C;
+  C* a = p->a.data();
+  C* b = p->b.data();
   if (p->r2c) {
-    for (int i = 0; i < h; ++i) {  // rows: real -> half spectrum
-      for (int j = 0; j < w; ++j) a[j] = p->real[(size_t)i * w + j];
+    // rows: two real rows ride one complex transform (z = x_i + i*x_{i+1}), separated afterwards by
+    // Hermitian symmetry: A[j] = (Z[j] + conj Z[w-j]) / 2, B[j] = (Z[j] - conj Z[w-j]) / (2i)
+    for (int i = 0; i < h; i += 2) {
+      const bool two = i + 1 < h;
+      const double* r0 = p->real + (size_t)i * w;
+      const double* r1 = r0 + w;
+      for (int j = 0; j < w; ++j) a[j] = C(r0[j], two ? r1[j] : 0.0);
       p->fw.exec(a, b, -1);
-      for (int j = 0; j < wh; ++j) p->cplx[(size_t)i * wh + j] = a[j];
+      C* o0 = p->cplx + (size_t)i * wh;
+      C* o1 = o0 + wh;
+      for (int j = 0; j < wh; ++j) {
+        const C z = a[j], zc = std::conj(a[j ? w - j : 0]);
+        o0[j] = 0.5 * (z + zc);
+        if (two) { const C d = z - zc; o1[j] = C(0.5 * d.imag(), -0.5 * d.real()); }
+      }
     }
     for (int j = 0; j < wh; ++j) {  // columns
       for (int i = 0; i < h; ++i) a[i] = p->cplx[(size_t)i * wh + j];
@@ -61,11 +73,20 @@ void fftw_execute(const fftw_plan p) {
       p->fh.exec(a, b, +1);
       for (int i = 0; i < h; ++i) p->cplx[(size_t)i * wh + j] = a[i];
     }
-    for (int i = 0; i < h; ++i) {
-      for (int j = 0; j < wh; ++j) a[j] = p->cplx[(size_t)i * wh + j];
-      for (int j = wh; j < w; ++j) a[j] = std::conj(p->cplx[(size_t)i * wh + (w - j)]);
+    // rows: two Hermitian half-spectra ride one complex backward transform (W = Y0 + i*Y1)
+    for (int i = 0; i < h; i += 2) {
+      const bool two = i + 1 < h;
+      const C* y0 = p->cplx + (size_t)i * wh;
+      const C* y1 = y0 + wh;
+      for (int j = 0; j < w; ++j) {
+        const C u = j < wh ? y0[j] : std::conj(y0[w - j]);
+        const C v = two ? (j < wh ? y1[j] : std::conj(y1[w - j])) : C(0, 0);
+        a[j] = C(u.real() - v.imag(), u.imag() + v.real());
+      }
       p->fw.exec(a, b, +1);
-      for (int j = 0; j < w; ++j) p->real[(size_t)i * w + j] = a[j].real();
+      double* r0 = p->real + (size_t)i * w;
+      double* r1 = r0 + w;
+      for (int j = 0; j < w; ++j) { r0[j] = a[j].real(); if (two) r1[j] = a[j].imag(); }
     }
   }
 }
