@@ -27,7 +27,7 @@ int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 // conv_direct.cu
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
-int occupancy_direct(int hk, size_t smem);
+int occupancy_direct(int hk, int hd, size_t smem);
 // conv_tuned108.cu
 size_t tuned108_smem_bytes();
 size_t tuned108_kspec_bytes();
@@ -140,6 +140,9 @@ constexpr int kPipe = 3;
 
 struct b2c_plan {
   Plan2D pl;
+  // an N x 1 column signal has the memory layout of a 1 x N row signal: planned and run as a row
+  // (coalesced lanes), reported back in the caller's orientation
+  bool transposed = false;
   int forced_path = B2C_PATH_AUTO;
   // lazily created device state (one device per plan)
   DeviceCtx* ctx = nullptr;
@@ -168,19 +171,29 @@ namespace {
 int work_ld(const Plan2D& pl) { return pl.w.P | 1; }
 size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (size_t)work_ld(pl); }
 
-// Cost-model crossover between the direct kernel and the FFT chain (refined by measurement,
-// see DESIGN.md): FP64 instruction estimates per image for both.
+// Crossover between the direct kernel and the FFT chain: two time models per image, fitted to the
+// measured sweep profiles/r01_crossover.csv (tools/crossover_sweep.py).
+//   direct: max(HBM stream at 3.0 TB/s, FMAs at 6.5 TFMA/s) for the 8-rows-per-thread variant,
+//           HBM at 2.5 TB/s + FMAs at 3.1 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image;
+//           kernels taller than 16 rows run a general variant that is about 4x slower.
+//   FFT   : planner cost units x 0.15 ps (generic kernel) or x 0.058 ps (tuned 108 x 108 kernel),
+//           never below 8 ns per image.
 int auto_path(const Plan2D& pl, bool shared) {
-  const double wkp = (pl.w.n_ker + 7) / 8 * 8, wdp = (pl.w.n_dst + 7) / 8 * 8;
-  const double direct = (double)pl.h.n_dst * wdp * pl.h.n_ker * wkp * 1.15;
+  const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
+  const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
+  double t_direct;
+  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / 3.0e12, fma / 6.5e12) + 4e-9;
+  else t_direct = bytes / 2.5e12 + fma / 3.1e12 + 4e-9;
+  if (pl.h.n_ker > 16) t_direct *= 4.0;
   const double rows = (double)pl.h.n_src + pl.h.lin;
-  double fft = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
-  if (shared) fft *= 0.5;  // two images per transform
-  fft *= 1.6;              // generic-path overhead (index arithmetic, barriers), measured factor
+  double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
+  if (shared) cost *= 0.5;  // two images per transform
+  const bool tuned = shared && pl.h.P == 108 && pl.w.P == 108 && pl.h.fold == 0 && pl.w.fold == 0;
+  const double t_fft = std::max(8e-9, cost * (tuned ? 0.058e-12 : 0.15e-12));
   // the direct kernel must also fit its tile in shared memory
   int spw;
-  if (direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, 8, &spw) > 200 * 1024) return B2C_PATH_FFT;
-  return direct <= fft ? B2C_PATH_DIRECT : B2C_PATH_FFT;
+  if (direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, std::min(8, pl.h.n_dst), &spw) > 200 * 1024) return B2C_PATH_FFT;
+  return t_direct <= t_fft ? B2C_PATH_DIRECT : B2C_PATH_FFT;
 }
 
 int ensure_device_state(b2c_plan* p) {
@@ -303,7 +316,7 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   q.tiles_per_image = (q.hd + tile - 1) / tile;
   const size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw);
   q.sp_w = spw;
-  int occ = occupancy_direct(q.hk, smem);
+  int occ = occupancy_direct(q.hk, q.hd, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);
@@ -382,6 +395,8 @@ int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kerne
   if ((long)h_src * w_src > (1L << 26) || (long)h_kernel * w_kernel > (1L << 26))
     return fail(B2C_ESIZE, "b2c_plan_create: image too large");
   b2c_plan* p = new b2c_plan();
+  p->transposed = (w_src == 1 && w_kernel == 1 && (h_src > 1 || h_kernel > 1));
+  if (p->transposed) { std::swap(h_src, w_src); std::swap(h_kernel, w_kernel); }
   if (!make_plan(mode, h_src, w_src, h_kernel, w_kernel, p->pl)) {
     delete p;
     return fail(B2C_EINVAL, "b2c_plan_create: planning failed");
@@ -397,10 +412,12 @@ int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kerne
 
 int b2c_plan_query(const b2c_plan* p, int* h_fft, int* w_fft, int* h_dst, int* w_dst) {
   if (!p) return fail(B2C_EINVAL, "b2c_plan_query: null plan");
-  if (h_fft) *h_fft = p->pl.empty ? 0 : p->pl.h.P;
-  if (w_fft) *w_fft = p->pl.empty ? 0 : p->pl.w.P;
-  if (h_dst) *h_dst = p->pl.empty ? 0 : p->pl.h.n_dst;
-  if (w_dst) *w_dst = p->pl.empty ? 0 : p->pl.w.n_dst;
+  const AxisPlan& ah = p->transposed ? p->pl.w : p->pl.h;
+  const AxisPlan& aw = p->transposed ? p->pl.h : p->pl.w;
+  if (h_fft) *h_fft = p->pl.empty ? 0 : ah.P;
+  if (w_fft) *w_fft = p->pl.empty ? 0 : aw.P;
+  if (h_dst) *h_dst = p->pl.empty ? 0 : ah.n_dst;
+  if (w_dst) *w_dst = p->pl.empty ? 0 : aw.n_dst;
   return 0;
 }
 
@@ -408,10 +425,12 @@ int b2c_plan_info(const b2c_plan* p, int* path, int* off_h, int* off_w, int* fol
                   long* wbytes, int* work_in_smem) {
   if (!p) return fail(B2C_EINVAL, "b2c_plan_info: null plan");
   if (path) *path = p->pl.empty ? B2C_PATH_AUTO : effective_path(p, 1);
-  if (off_h) *off_h = p->pl.h.off;
-  if (off_w) *off_w = p->pl.w.off;
-  if (fold_h) *fold_h = p->pl.h.fold;
-  if (fold_w) *fold_w = p->pl.w.fold;
+  const AxisPlan& ah = p->transposed ? p->pl.w : p->pl.h;
+  const AxisPlan& aw = p->transposed ? p->pl.h : p->pl.w;
+  if (off_h) *off_h = ah.off;
+  if (off_w) *off_w = aw.off;
+  if (fold_h) *fold_h = ah.fold;
+  if (fold_w) *fold_w = aw.fold;
   if (wbytes) *wbytes = p->pl.empty ? 0 : (long)work_bytes(p->pl);
   if (work_in_smem) *work_in_smem = p->pl.empty ? 0 : (work_bytes(p->pl) <= 232448 ? 1 : 0);
   return 0;

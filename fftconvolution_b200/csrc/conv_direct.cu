@@ -16,7 +16,6 @@ namespace b2c {
 
 extern __shared__ __align__(16) unsigned char b2c_smem_direct[];
 
-constexpr int TI = 8;
 constexpr int kMaxDirectHK = 16;
 constexpr int kDirectThreads = 256;
 
@@ -26,7 +25,8 @@ __device__ __forceinline__ int wrap_index(int x, int m) {
 }
 
 // HK > 0: compile-time kernel height; HK == 0: run-time height (general variant).
-template <int HK>
+// TI: output rows per thread (8 for images, 1 for 1-D row signals and very short images).
+template <int HK, int TI>
 __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_constant__ DirectParams p) {
   double* kflip = reinterpret_cast<double*>(b2c_smem_direct);   // [wk][hk_pad]: column-major, flipped
   const int hk = HK > 0 ? HK : p.hk;
@@ -139,28 +139,29 @@ size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out) {
 typedef void (*direct_fn)(const DirectParams);
 
 template <int HK>
-static direct_fn pick() { return direct_kernel<HK>; }
+static direct_fn pick(bool tall) { return tall ? direct_kernel<HK, 8> : direct_kernel<HK, 1>; }
 
-static direct_fn direct_variant(int hk) {
+static direct_fn direct_variant(int hk, int hd) {
+  const bool tall = hd >= 8;
   switch (hk) {
-    case 1: return pick<1>();   case 2: return pick<2>();   case 3: return pick<3>();   case 4: return pick<4>();
-    case 5: return pick<5>();   case 6: return pick<6>();   case 7: return pick<7>();   case 8: return pick<8>();
-    case 9: return pick<9>();   case 10: return pick<10>(); case 11: return pick<11>(); case 12: return pick<12>();
-    case 13: return pick<13>(); case 14: return pick<14>(); case 15: return pick<15>(); case 16: return pick<16>();
+    case 1: return pick<1>(tall);   case 2: return pick<2>(tall);   case 3: return pick<3>(tall);   case 4: return pick<4>(tall);
+    case 5: return pick<5>(tall);   case 6: return pick<6>(tall);   case 7: return pick<7>(tall);   case 8: return pick<8>(tall);
+    case 9: return pick<9>(tall);   case 10: return pick<10>(tall); case 11: return pick<11>(tall); case 12: return pick<12>(tall);
+    case 13: return pick<13>(tall); case 14: return pick<14>(tall); case 15: return pick<15>(tall); case 16: return pick<16>(tall);
   }
-  return pick<0>();
+  return pick<0>(tall);
 }
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
-  direct_fn fn = direct_variant(p.hk);
+  direct_fn fn = direct_variant(p.hk, p.hd);
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   fn<<<grid, kDirectThreads, smem, st>>>(p);
   return cudaGetLastError();
 }
 
-int occupancy_direct(int hk, size_t smem) {
+int occupancy_direct(int hk, int hd, size_t smem) {
   int n = 0;
-  direct_fn fn = direct_variant(hk);
+  direct_fn fn = direct_variant(hk, hd);
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
   return n;
