@@ -28,6 +28,8 @@ int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
 int occupancy_direct(int hk, int hd, size_t smem);
+// conv_big2d.cu
+cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 // conv_tuned108.cu
 size_t tuned108_smem_bytes();
 size_t tuned108_kspec_bytes();
@@ -68,6 +70,7 @@ int fail(int code, const char* fmt, ...) {
 struct AxisTables {
   cplx* tw = nullptr;
   int* neg = nullptr;
+  int* posf = nullptr;
 };
 
 // Per-device cache: twiddle / partner tables keyed by period (cheap plan creation: the
@@ -117,8 +120,10 @@ int get_tables(DeviceCtx* c, const AxisPlan& a, AxisTables* out) {
   AxisTables t;
   CUDA_TRY(cudaMalloc(&t.tw, sizeof(cplx) * P));
   CUDA_TRY(cudaMalloc(&t.neg, sizeof(int) * P));
+  CUDA_TRY(cudaMalloc(&t.posf, sizeof(int) * P));
   CUDA_TRY(cudaMemcpy(t.tw, tw.data(), sizeof(cplx) * P, cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(t.neg, neg.data(), sizeof(int) * P, cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(t.posf, pos_of.data(), sizeof(int) * P, cudaMemcpyHostToDevice));
   c->tables[P] = t;
   *out = t;
   return 0;
@@ -150,6 +155,7 @@ struct b2c_plan {
   cplx* kspec = nullptr;
   cplx* work = nullptr;
   size_t work_slabs = 0;
+  size_t work_slab_bytes = 0;
   // single-image host path staging
   double* d_one = nullptr;
   size_t d_one_bytes = 0;
@@ -176,7 +182,7 @@ size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (si
 //   direct: max(HBM stream at 3.0 TB/s, FMAs at 6.5 TFMA/s) for the 8-rows-per-thread variant,
 //           HBM at 2.5 TB/s + FMAs at 3.1 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image;
 //           kernels taller than 16 rows run a general variant that is about 4x slower.
-//   FFT   : planner cost units x 0.15 ps (generic kernel) or x 0.058 ps (tuned 108 x 108 kernel),
+//   FFT   : planner cost units x 0.15 ps (generic kernel) or x 0.047 ps (tuned 108 x 108 kernel),
 //           never below 8 ns per image.
 int auto_path(const Plan2D& pl, bool shared) {
   const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
@@ -189,7 +195,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
   if (shared) cost *= 0.5;  // two images per transform
   const bool tuned = shared && pl.h.P == 108 && pl.w.P == 108 && pl.h.fold == 0 && pl.w.fold == 0;
-  const double t_fft = std::max(8e-9, cost * (tuned ? 0.058e-12 : 0.15e-12));
+  const double t_fft = std::max(8e-9, cost * (tuned ? 0.047e-12 : 0.15e-12));
   // the direct kernel must also fit its tile in shared memory
   int spw;
   if (direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, std::min(8, pl.h.n_dst), &spw) > 200 * 1024) return B2C_PATH_FFT;
@@ -212,6 +218,7 @@ void fill_axis(AxisDev& d, const AxisPlan& a, const AxisTables& t) {
   for (int i = 0; i < 16; ++i) d.radix[i] = i < a.nstages ? a.radix[i] : 0;
   d.tw = t.tw;
   d.neg = t.neg;
+  d.posf = t.posf;
 }
 
 // Shared-kernel plans whose periods are 108 x 108 run on the tuned kernel (conv_tuned108.cu).
@@ -241,11 +248,67 @@ int run_tuned108(b2c_plan* p, const double* d_src, const double* d_ker, double* 
   return 0;
 }
 
+// Plans whose full complex work buffer exceeds shared memory run in strip mode (conv_big2d.cu):
+// row chunks / column strips in shared memory, half spectra through an L2-resident slab.
+int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst, long n,
+              cudaStream_t st) {
+  const Plan2D& pl = p->pl;
+  const size_t smem_max = (size_t)p->ctx->smem_optin;
+  BigParams q;
+  memset(&q, 0, sizeof q);
+  q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
+  q.hd = pl.h.n_dst; q.wd = pl.w.n_dst; q.off_h = pl.h.off; q.off_w = pl.w.off;
+  q.kwrap_h = pl.h.kwrap; q.kwrap_w = pl.w.kwrap;
+  const int Ph = pl.h.P, Pw = pl.w.P;
+  q.half_w = Pw / 2 + 1;
+  q.ldw = Pw | 1;
+  const int hke = std::min(q.hk, q.kwrap_h);
+  const int rows_in = std::max(q.hs, hke), pairs = (q.hd + 1) / 2;
+  const int max_rows = (int)(smem_max / (sizeof(cplx) * q.ldw));
+  const int max_cols = ((int)(smem_max / (sizeof(cplx) * Ph)) - 1) / 2;
+  if (max_rows < 1 || max_cols < 1)
+    return fail(B2C_ESIZE, "transform of %d x %d points is too large for the strip-mode kernel", Ph, Pw);
+  const int most_rows = std::max(rows_in, pairs);
+  const int nchunks = (most_rows + max_rows - 1) / max_rows;
+  q.rows_chunk = (most_rows + nchunks - 1) / nchunks;          // balanced chunks
+  const int nstrips = (q.half_w + max_cols - 1) / max_cols;
+  q.cols_strip = (q.half_w + nstrips - 1) / nstrips;
+  q.ldc = 2 * q.cols_strip + 1;
+  q.rows_y = q.off_h + q.hd;
+  fill_axis(q.ah, pl.h, p->th);
+  fill_axis(q.aw, pl.w, p->tw);
+  q.scale = 1.0 / ((double)Ph * (double)Pw);
+  q.src = d_src; q.ker = d_ker; q.ker_stride = shared ? 0 : (long)q.hk * q.wk; q.dst = d_dst; q.n_images = n;
+  const size_t smem = sizeof(cplx) * std::max((size_t)q.rows_chunk * q.ldw, (size_t)Ph * q.ldc);
+  const int grid = (int)std::max<long>(1, std::min<long>(n, p->ctx->sms));
+  const size_t slab_per_cta = sizeof(cplx) * (size_t)(q.hs + hke + q.rows_y) * q.half_w;
+  const size_t slabs = (size_t)p->ctx->sms;
+  if (p->work_slabs < slabs || p->work_slab_bytes < slab_per_cta) {
+    if (p->work) cudaFree(p->work);
+    p->work = nullptr; p->work_slabs = 0; p->work_slab_bytes = 0;
+    CUDA_TRY(cudaMalloc(&p->work, slab_per_cta * slabs));
+    p->work_slabs = slabs; p->work_slab_bytes = slab_per_cta;
+  }
+  q.slab = p->work;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_timer.on && g_timer.ev.size() < 8192) {
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, st));
+  }
+  CUDA_TRY(launch_conv_big2d(q, grid, smem, st));
+  ++g_launches;
+  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  return 0;
+}
+
 int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst,
                  long n, cudaStream_t st) {
   if (int rc = ensure_device_state(p)) return rc;
   const Plan2D& pl = p->pl;
   if (tuned108_applies(p, shared)) return run_tuned108(p, d_src, d_ker, d_dst, n, st);
+  if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&
+      p->forced_path != B2C_PATH_FFT_GENERIC)
+    return run_big2d(p, d_src, d_ker, shared, d_dst, n, st);
   ConvParams q;
   memset(&q, 0, sizeof q);
   q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
@@ -268,11 +331,11 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
   if (grid < 1) grid = 1;
   if (!q.work_in_smem) {
     const size_t slabs = (size_t)std::max(grid, 1);
-    if (p->work_slabs < slabs) {
+    if (p->work_slabs < slabs || p->work_slab_bytes < wb) {
       if (p->work) cudaFree(p->work);
-      p->work = nullptr; p->work_slabs = 0;
+      p->work = nullptr; p->work_slabs = 0; p->work_slab_bytes = 0;
       CUDA_TRY(cudaMalloc(&p->work, wb * (size_t)p->ctx->sms * occ));
-      p->work_slabs = (size_t)p->ctx->sms * occ;
+      p->work_slabs = (size_t)p->ctx->sms * occ; p->work_slab_bytes = wb;
     }
     q.work = p->work;
   }

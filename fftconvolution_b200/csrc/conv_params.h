@@ -39,4 +39,25 @@ struct DirectParams {
   long n_images;
 };
 
+// strip-mode kernel (conv_big2d.cu)
+struct BigParams {
+  int hs, ws, hk, wk, hd, wd;
+  int off_h, off_w;
+  int kwrap_h, kwrap_w;
+  int half_w;        // P_w / 2 + 1 half-spectrum columns
+  int ldw;           // row pitch (complex) of the row-phase buffer, odd
+  int rows_chunk;    // rows per row-phase chunk
+  int cols_strip;    // half-spectrum columns per column-phase strip
+  int ldc;           // row pitch (complex) of the column-phase buffer = 2*cols_strip (+1)
+  int rows_y;        // rows of the linear result that are produced: off_h + hd
+  AxisDev ah, aw;
+  double scale;
+  const double* src;
+  const double* ker;
+  long ker_stride;   // 0: one shared kernel
+  double* dst;
+  long n_images;
+  cplx* slab;        // [gridDim.x][(hs + hke + rows_y) * half_w]
+};
+
 }  // namespace b2c

@@ -224,6 +224,7 @@ struct AxisDev {
   int radix[16];
   const cplx* tw;   // exp(-2*pi*i*k/P)
   const int* neg;   // neg[pos] = position holding frequency (-freq(pos)) mod P   (scrambled order)
+  const int* posf;  // posf[k]  = position holding frequency k
 };
 
 // Forward transform of `nlines` lines (starting at W, i.e. the caller offsets W to the first line).
@@ -232,10 +233,10 @@ __device__ __forceinline__ void fft_forward(const AxisDev& ax, cplx* W, int es, 
   int n = ax.P;
   for (int s = 0; s < ax.nstages; ++s) {
     const int R = ax.radix[s];
-    // row-like axis (es == 1): adjacent lanes walk the butterfly index while its stride m is long
-    // enough to be contiguous; for the last, short-stride stages they walk adjacent lines instead
-    // (stride ls, odd by construction -> no bank conflicts)
-    const bool stage_lf = lf || (n / R < 8 && nlines >= 8);
+    // row-like axis (es == 1): with enough lines, adjacent lanes walk adjacent LINES (stride ls, odd
+    // by construction -> no bank conflicts) so that a warp shares one butterfly index and its
+    // twiddles are a single broadcast read; with few lines (1-D signals) lanes walk the butterfly index
+    const bool stage_lf = lf || nlines >= 16 || (n / R < 8 && nlines >= 8);
     fft_stage_dispatch<false>(R, W, es, ls, nlines, ax.P, n, ax.tw, stage_lf);
     n /= R;
     __syncthreads();
@@ -248,7 +249,7 @@ __device__ __forceinline__ void fft_backward(const AxisDev& ax, cplx* W, int es,
   for (int s = ax.nstages - 1; s >= 0; --s) {
     const int R = ax.radix[s];
     n *= R;
-    const bool stage_lf = lf || (n / R < 8 && nlines >= 8);
+    const bool stage_lf = lf || nlines >= 16 || (n / R < 8 && nlines >= 8);
     fft_stage_dispatch<true>(R, W, es, ls, nlines, ax.P, n, ax.tw, stage_lf);
     __syncthreads();
   }
