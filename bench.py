@@ -302,7 +302,8 @@ def run_b2c_arm(args):
     achieved = (n_local * ALGO_BYTES_PER_CONV / kernel_s) / 1e9 if kernel_s > 0 else None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(),
-                "peak_kind": peak_kind, "kernel": "conv_shared_kernel", "kernel_ms": avg_ms.value,
+                "peak_kind": peak_kind,
+                "kernel": "b2c::t108::conv_kernel" if (plan.h_fft, plan.w_fft) == (108, 108) else "b2c::conv_shared_kernel", "kernel_ms": avg_ms.value,
                 "kernel_launches": nl.value, "algorithmic_bytes_per_launch": n_local * ALGO_BYTES_PER_CONV}
 
     cpu_baseline = None
