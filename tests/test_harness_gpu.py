@@ -15,10 +15,17 @@ TEST_BIN = os.path.join(ROOT, "oracle", "_ref", "convolution_test_b2c.bin")
 BENCH_BIN = os.path.join(ROOT, "oracle", "_ref", "convolution_benchmark_b2c.bin")
 
 
-def test_reference_test_driver_passes_unchanged(tmp_path):
-    if not os.path.exists(TEST_BIN):
-        pytest.skip("oracle/_ref/convolution_test_b2c.bin was not built (reference sources absent at build time)")
-    r = subprocess.run([TEST_BIN], cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=600)
+GSL_TEST_BIN = os.path.join(ROOT, "oracle", "_ref", "convolution_test_gsl_b2c.bin")
+
+
+@pytest.mark.parametrize("flavour", ["fftw", "gsl"])
+def test_reference_test_driver_passes_unchanged(tmp_path, flavour):
+    """-DCONVOLUTION=0 against include/convolution_fftw.h and -DCONVOLUTION=1 against the alias header
+    include/convolution_gsl.h (the reference's two FFT back ends share one interface)."""
+    binary = TEST_BIN if flavour == "fftw" else GSL_TEST_BIN
+    if not os.path.exists(binary):
+        pytest.skip("%s was not built (reference sources absent at build time)" % binary)
+    r = subprocess.run([binary], cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=600)
     out = r.stdout.decode("utf-8", "replace")
     assert r.returncode == 0, out[-2000:]
     passed = re.findall(r"All tests passed for ([a-z_ ]+?) (\d+) / (\d+)", out)
@@ -27,7 +34,7 @@ def test_reference_test_driver_passes_unchanged(tmp_path):
     # 9 categories x {full, same, valid, circular full, same unpadded, circular full unpadded}
     assert len(passed) == 54, (len(passed), out[-2000:])
     assert all(a == b == "50" for _, a, b in passed)
-    log = open(os.path.join(tmp_path, "convolution_test_fftw.log")).read()
+    log = open(os.path.join(tmp_path, "convolution_test_%s.log" % flavour)).read()
     assert log.count("PASSED") == 54 * 50 and "FAILED" not in log
 
 
