@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -581,9 +582,11 @@ int b2c_convolve_batch_host(b2c_plan* p, const double* src, const double* kernel
     }
     p->pipe_ready = true;
   }
-  // chunk: ~48 MB of traffic per stage keeps the three engines busy without hoarding HBM
+  // chunk: ~128 MB of traffic per stage (measured best on PCIe Gen5: 45.9 GB/s each way, tools/bench_e2e.py)
   const size_t per_img = sizeof(double) * (sn + dn + (kernel_is_shared ? 0 : kn));
-  long chunk = (long)std::max<size_t>(2, (48u << 20) / std::max<size_t>(per_img, 1));
+  size_t pipe_bytes = 128u << 20;
+  if (const char* e = getenv("B2C_PIPE_MB")) pipe_bytes = (size_t)std::max(1, atoi(e)) << 20;   // tuning knob
+  long chunk = (long)std::max<size_t>(2, pipe_bytes / std::max<size_t>(per_img, 1));
   chunk = std::min(chunk, n_images);
   if (chunk & 1) ++chunk;  // keep image pairs together
   if (p->pipe_chunk < chunk || p->pipe_shared != kernel_is_shared) {

@@ -178,7 +178,7 @@ __device__ __forceinline__ void fft_stage(cplx* W, int es, int ls, int nlines, i
     else { line = fast_div(task, per_line, inv_per); t = task - line * per_line; }
     const int b = fast_div(t, m, inv_m);
     const int j = t - b * m;
-    cplx* p = W + (size_t)line * ls + (size_t)(b * n + j) * es;
+    cplx* p = W + (line * ls + (b * n + j) * es);   // 32-bit offsets: a work buffer has < 2^24 elements
     const int stride = m * es;
     cplx v[R];
 #pragma unroll
