@@ -204,7 +204,14 @@ int auto_path(const Plan2D& pl, bool shared) {
 }
 
 int ensure_device_state(b2c_plan* p) {
-  if (p->ctx) return 0;
+  if (p->ctx) {   // a plan's scratch lives on the device of its first compute call
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev != p->ctx->dev)
+      return fail(B2C_EINVAL, "plan was first used on device %d but the current device is %d: create one plan per device",
+                  p->ctx->dev, dev);
+    return 0;
+  }
   DeviceCtx* c = nullptr;
   if (int rc = get_ctx(&c)) return rc;
   if (int rc = get_tables(c, p->pl.h, &p->th)) return rc;
