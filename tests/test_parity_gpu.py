@@ -263,3 +263,52 @@ def test_tuned_108_kernel_vs_oracle_and_generic(b2c, oracle, torch_cuda):
         _check(g.convolve_host(src[0], ker), got[0], ("generic == tuned", mode))
         one = p.convolve_host(src[3], ker)
         assert np.array_equal(one, got[3]), "batch result must not depend on batch position"
+
+
+def test_batch_edges_and_errors(b2c, oracle, torch_cuda):
+    """Empty batch, batch of one, odd batch tails on every kernel family, and argument errors."""
+    torch = torch_cuda
+    rng = np.random.default_rng(31)
+    L = b2c.lib()
+    for (mode, hs, ws, hk, wk, path) in [(2, 100, 100, 15, 15, b2c.PATH_FFT), (0, 20, 30, 5, 7, b2c.PATH_FFT_GENERIC),
+                                         (2, 40, 40, 5, 5, b2c.PATH_DIRECT), (7, 120, 90, 110, 130, b2c.PATH_FFT)]:
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        p.set_path(path)
+        for n in (0, 1, 3):
+            src = rng.random((max(n, 1), hs, ws)); ker = rng.random((hk, wk))
+            d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+            d_dst = torch.full((max(n, 1), p.h_dst, p.w_dst), -7.0, dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+            torch.cuda.synchronize()
+            got = d_dst.cpu().numpy()
+            for i in range(n):
+                _check(got[i], oracle.convolve_direct8(mode, src[i], ker), ("edge batch", mode, n, i))
+            assert np.all(got[n:] == -7.0), "images beyond the batch must stay untouched"
+        import ctypes
+        assert L.b2c_convolve_batch_device(p._h, None, None, 1, None, 4, None) == 1      # null buffers
+        assert L.b2c_convolve_batch_device(p._h, None, None, 1, None, -1, None) == 1     # negative batch
+        p.destroy()
+    assert L.b2c_convolve_host(None, None, None, None) == 1
+    assert b"null plan" in L.b2c_last_error()
+
+
+def test_strip_mode_shared_kernel_and_rectangles(b2c, oracle, torch_cuda):
+    """Transforms larger than shared memory (conv_big2d.cu) with a shared kernel, rectangular sizes
+    and every crop mode; CIRCULAR_SAME with a non-smooth size falls back to the slab path (fold)."""
+    torch = torch_cuda
+    rng = np.random.default_rng(32)
+    for (mode, hs, ws, hk, wk) in [(0, 150, 130, 31, 60), (2, 170, 90, 40, 120), (3, 160, 170, 9, 30), (5, 128, 128, 64, 33),
+                                   (4, 131, 127, 20, 25)]:
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        assert not p.info()["work_in_smem"], (mode, hs, ws, hk, wk, p.h_fft, p.w_fft)
+        p.set_path(b2c.PATH_FFT)
+        n = 3
+        src, ker = rng.random((n, hs, ws)), rng.random((hk, wk))
+        d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+        d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+        p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+        torch.cuda.synchronize()
+        got = d_dst.cpu().numpy()
+        for i in range(n):
+            _check(got[i], oracle.convolve_direct8(mode, src[i], ker), ("strip mode", mode, hs, ws, hk, wk, i))
+        p.destroy()
