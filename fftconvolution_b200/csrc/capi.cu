@@ -38,6 +38,12 @@ int tuned108_occupancy();
 cudaError_t launch_tuned108_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st);
 cudaError_t launch_tuned108_conv(int hs, int ws, int hd, int wd, int off_h, int off_w, const double* d_src,
                                  double* d_dst, long n, const cplx* kspec, const cplx* tw, int grid, cudaStream_t st);
+// conv_tuned2.cu
+bool tuned2_has(int P);
+size_t tuned2_kspec_bytes(int P);
+cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
+                          const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kspec,
+                          const cplx* tw, int sms, cudaStream_t st, int* launches);
 // util_kernels.cu
 cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long first, cudaStream_t st);
 cudaError_t launch_checksum(const double* d, long n, unsigned long long* d_out3, cudaStream_t st);
@@ -195,7 +201,8 @@ int auto_path(const Plan2D& pl, bool shared) {
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
   if (shared) cost *= 0.5;  // two images per transform
-  const bool tuned = shared && pl.h.P == 108 && pl.w.P == 108 && pl.h.fold == 0 && pl.w.fold == 0;
+  const bool tuned = shared && pl.h.P == pl.w.P && (pl.h.P == 108 || tuned2_has(pl.h.P)) && pl.h.fold == 0 &&
+                     pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
   const double t_fft = std::max(8e-9, cost * (tuned ? 0.047e-12 : 0.15e-12));
   // the direct kernel must also fit its tile in shared memory
   int spw;
@@ -309,11 +316,35 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
   return 0;
 }
 
+// Shared-kernel plans with equal periods from the tuned menu (conv_tuned2.cu).
+bool tuned2_applies(const b2c_plan* p, int shared) {
+  const Plan2D& pl = p->pl;
+  return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == pl.w.P && tuned2_has(pl.h.P) &&
+         pl.h.fold == 0 && pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
+}
+
+int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
+  const Plan2D& pl = p->pl;
+  if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, std::max(work_bytes(pl), tuned2_kspec_bytes(pl.h.P))));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_timer.on && g_timer.ev.size() < 8192) {
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, st));
+  }
+  int launches = 0;
+  CUDA_TRY(launch_tuned2(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
+                         pl.w.off, d_src, d_ker, d_dst, n, p->kspec, p->tw.tw, p->ctx->sms, st, &launches));
+  g_launches += launches;
+  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  return 0;
+}
+
 int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst,
                  long n, cudaStream_t st) {
   if (int rc = ensure_device_state(p)) return rc;
   const Plan2D& pl = p->pl;
   if (tuned108_applies(p, shared)) return run_tuned108(p, d_src, d_ker, d_dst, n, st);
+  if (tuned2_applies(p, shared)) return run_tuned2(p, d_src, d_ker, d_dst, n, st);
   if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&
       p->forced_path != B2C_PATH_FFT_GENERIC)
     return run_big2d(p, d_src, d_ker, shared, d_dst, n, st);

@@ -176,6 +176,20 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
       if (ph == 108 && pw == 108) c *= 0.3;  // hand-tuned 108 x 108 kernel (conv_tuned108.cu), measured
       if (best < 0 || c < best) { best = c; out.h.P = ph; out.w.P = pw; }
     }
+  // square periods that have a hand-tuned kernel (conv_tuned108.cu, conv_tuned2.cu): one period for
+  // both axes, about a third of the generic kernel's time at equal size (measured)
+  if (!out.h.exact && !out.w.exact && out.h.fold == 0 && out.w.fold == 0 && hs > 1 && ws > 1) {
+    static const int menu[] = {40, 48, 56, 64, 72, 80, 90, 96, 100, 108, 112, 120, 128};
+    const int need = std::max(out.h.min_period, out.w.min_period);
+    for (int pm : menu) {
+      if (pm < need) continue;
+      // all tuned kernels share one seven-pass structure: their time scales with the P*P points moved,
+      // anchored at 0.3 x the generic model for the measured 108 x 108 case
+      static const double alpha = 0.3 * (424.0 * fft_cost(108) + 12.0 * 108 * 108) / (108.0 * 108.0);
+      const double c = alpha * pm * pm;
+      if (c < best) { best = c; out.h.P = pm; out.w.P = pm; }
+    }
+  }
   for (AxisPlan* a : {&out.h, &out.w}) {
     if (a->kwrap == 0) a->kwrap = a->P;
     a->n_ker_eff = std::min(a->n_ker, a->kwrap);

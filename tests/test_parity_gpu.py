@@ -312,3 +312,39 @@ def test_strip_mode_shared_kernel_and_rectangles(b2c, oracle, torch_cuda):
         for i in range(n):
             _check(got[i], oracle.convolve_direct8(mode, src[i], ker), ("strip mode", mode, hs, ws, hk, wk, i))
         p.destroy()
+
+
+def test_tuned_square_period_family_vs_oracle(b2c, oracle, torch_cuda):
+    """conv_tuned2.cu: one fused kernel per square period of the menu (40 ... 128).  Each period is hit
+    with several modes / rectangular shapes and checked against the oracle and the any-size kernel."""
+    torch = torch_cuda
+    rng = np.random.default_rng(41)
+    menu = [40, 48, 56, 64, 72, 80, 90, 96, 100, 112, 120, 128]
+    hit = set()
+    for P in menu:
+        shapes = [(b2c.LINEAR_FULL, P - 9, P - 13, 10, 14),            # full length == P on both axes
+                  (b2c.LINEAR_SAME, P - 4, P - 7, 9, 15),              # needs P-4+4, P-7+7
+                  (b2c.LINEAR_VALID, P, P - 3, 5, 3),
+                  (b2c.CIRCULAR_SAME_PADDED, P - 20, P - 11, 21, 12),
+                  (b2c.CIRCULAR_FULL, P // 2, P // 2 + 1, P // 2 + 1, P // 2)]
+        for mode, hs, ws, hk, wk in shapes:
+            p = b2c.Plan(mode, hs, ws, hk, wk)
+            if (p.h_fft, p.w_fft) != (P, P):
+                p.destroy()
+                continue
+            hit.add(P)
+            p.set_path(b2c.PATH_FFT)
+            n = 3
+            src, ker = rng.random((n, hs, ws)), rng.random((hk, wk))
+            d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+            d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+            torch.cuda.synchronize()
+            got = d_dst.cpu().numpy()
+            for i in range(n):
+                _check(got[i], oracle.convolve_direct8(mode, src[i], ker), ("tuned2", P, mode, hs, ws, hk, wk, i))
+            g = b2c.Plan(mode, hs, ws, hk, wk)
+            g.set_path(b2c.PATH_FFT_GENERIC)
+            _check(g.convolve_host(src[1], ker), got[1], ("generic == tuned2", P, mode))
+            p.destroy(); g.destroy()
+    assert hit == set(menu), sorted(set(menu) - hit)
