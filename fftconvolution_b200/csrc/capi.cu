@@ -186,16 +186,16 @@ size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (si
 
 // Crossover between the direct kernel and the FFT chain: two time models per image, fitted to the
 // measured sweep profiles/r01_crossover.csv (tools/crossover_sweep.py).
-//   direct: max(HBM stream at 3.0 TB/s, FMAs at 6.5 TFMA/s) for the 8-rows-per-thread variant,
+//   direct: max(HBM stream at 3.0 TB/s, FMAs at 5.8 TFMA/s) for the 8-rows-per-thread variant,
 //           HBM at 2.5 TB/s + FMAs at 3.1 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image;
 //           kernels taller than 16 rows run a general variant that is about 4x slower.
-//   FFT   : planner cost units x 0.15 ps (generic kernel) or x 0.047 ps (tuned 108 x 108 kernel),
-//           never below 8 ns per image.
+//   FFT   : planner cost units x 0.15 ps, never below 8 ns per image (generic kernel); 6.5 ps per point
+//           of the period + 3 ns for the tuned square-period kernels.
 int auto_path(const Plan2D& pl, bool shared) {
   const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
   const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
   double t_direct;
-  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / 3.0e12, fma / 6.5e12) + 4e-9;
+  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / 3.0e12, fma / 5.8e12) + 4e-9;
   else t_direct = bytes / 2.5e12 + fma / 3.1e12 + 4e-9;
   if (pl.h.n_ker > 16) t_direct *= 4.0;
   const double rows = (double)pl.h.n_src + pl.h.lin;
@@ -203,7 +203,9 @@ int auto_path(const Plan2D& pl, bool shared) {
   if (shared) cost *= 0.5;  // two images per transform
   const bool tuned = shared && pl.h.P == pl.w.P && (pl.h.P == 108 || tuned2_has(pl.h.P)) && pl.h.fold == 0 &&
                      pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
-  const double t_fft = std::max(8e-9, cost * (tuned ? 0.047e-12 : 0.15e-12));
+  // tuned kernels: 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 3 ns
+  const double pp = (double)pl.h.P * pl.w.P;
+  const double t_fft = tuned ? 6.5e-12 * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 3e-9 : std::max(8e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
   int spw;
   if (direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, std::min(8, pl.h.n_dst), &spw) > 200 * 1024) return B2C_PATH_FFT;
