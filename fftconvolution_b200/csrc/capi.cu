@@ -31,6 +31,9 @@ cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStre
 int occupancy_direct(int hk, int hd, size_t smem);
 // conv_big2d.cu
 cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
+// conv_big2ds.cu
+bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, int ns_w);
+cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 // conv_tuned108.cu
 size_t tuned108_smem_bytes();
 size_t tuned108_kspec_bytes();
@@ -288,8 +291,10 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
   const int most_rows = std::max(rows_in, pairs);
   const int nchunks = (most_rows + max_rows - 1) / max_rows;
   q.rows_chunk = (most_rows + nchunks - 1) / nchunks;          // balanced chunks
+  if (q.rows_chunk > 32) q.rows_chunk = std::min(max_rows, (q.rows_chunk + 31) / 32 * 32);   // whole warps of lines
   const int nstrips = (q.half_w + max_cols - 1) / max_cols;
   q.cols_strip = (q.half_w + nstrips - 1) / nstrips;
+  if (max_cols >= 32 && q.cols_strip > 16) q.cols_strip = std::min(max_cols, (q.cols_strip + 31) / 32 * 32) >= 32 ? 32 * std::max(1, std::min(max_cols, (q.cols_strip + 31) / 32 * 32) / 32) : q.cols_strip;
   q.ldc = 2 * q.cols_strip + 1;
   q.rows_y = q.off_h + q.hd;
   fill_axis(q.ah, pl.h, p->th);
@@ -312,7 +317,8 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
     CUDA_TRY(cudaEventRecord(e0, st));
   }
-  CUDA_TRY(launch_conv_big2d(q, grid, smem, st));
+  if (big2ds_has(Ph, Pw, pl.h.radix, pl.h.nstages, pl.w.radix, pl.w.nstages)) CUDA_TRY(launch_conv_big2ds(q, grid, smem, st));
+  else CUDA_TRY(launch_conv_big2d(q, grid, smem, st));
   ++g_launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
   return 0;
