@@ -273,13 +273,14 @@ int run_tuned108(b2c_plan* p, const double* d_src, const double* d_ker, double* 
 int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst, long n,
               cudaStream_t st) {
   const Plan2D& pl = p->pl;
+  const int Ph = pl.h.P, Pw = pl.w.P;
+  const bool tuned = big2ds_has(Ph, Pw, pl.h.radix, pl.h.nstages, pl.w.radix, pl.w.nstages);
   const size_t smem_max = (size_t)p->ctx->smem_optin;
   BigParams q;
   memset(&q, 0, sizeof q);
   q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
   q.hd = pl.h.n_dst; q.wd = pl.w.n_dst; q.off_h = pl.h.off; q.off_w = pl.w.off;
   q.kwrap_h = pl.h.kwrap; q.kwrap_w = pl.w.kwrap;
-  const int Ph = pl.h.P, Pw = pl.w.P;
   q.half_w = Pw / 2 + 1;
   q.ldw = Pw | 1;
   const int hke = std::min(q.hk, q.kwrap_h);
@@ -294,16 +295,19 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
   if (q.rows_chunk > 32) q.rows_chunk = std::min(max_rows, (q.rows_chunk + 31) / 32 * 32);   // whole warps of lines
   const int nstrips = (q.half_w + max_cols - 1) / max_cols;
   q.cols_strip = (q.half_w + nstrips - 1) / nstrips;
-  if (max_cols >= 32 && q.cols_strip > 16) q.cols_strip = std::min(max_cols, (q.cols_strip + 31) / 32 * 32) >= 32 ? 32 * std::max(1, std::min(max_cols, (q.cols_strip + 31) / 32 * 32) / 32) : q.cols_strip;
+  // whole warps of lines in the column phase (a strip holds 2 * cols_strip lines)
+  if (max_cols >= 32 && q.cols_strip > 16) q.cols_strip = std::min(max_cols / 32 * 32, (q.cols_strip + 31) / 32 * 32);
+  else if (max_cols >= 16 && q.cols_strip > 8) q.cols_strip = 16;
   q.ldc = 2 * q.cols_strip + 1;
   q.rows_y = q.off_h + q.hd;
   fill_axis(q.ah, pl.h, p->th);
   fill_axis(q.aw, pl.w, p->tw);
   q.scale = 1.0 / ((double)Ph * (double)Pw);
   q.src = d_src; q.ker = d_ker; q.ker_stride = shared ? 0 : (long)q.hk * q.wk; q.dst = d_dst; q.n_images = n;
+  if (tuned) { q.cols_strip = 32; q.ldc = 64; }   // conv_big2ds.cu: fixed strips, S and K columns in two dense arrays
   const size_t smem = sizeof(cplx) * std::max((size_t)q.rows_chunk * q.ldw, (size_t)Ph * q.ldc);
-  const int grid = (int)std::max<long>(1, std::min<long>(n, p->ctx->sms));
-  const size_t slab_per_cta = sizeof(cplx) * (size_t)(q.hs + hke + q.rows_y) * q.half_w;
+  const int grid = (int)std::max<long>(1, std::min<long>(n, (long)p->ctx->sms));
+  const size_t slab_per_cta = sizeof(cplx) * (size_t)std::max(q.hs + hke, q.rows_y) * q.half_w;   // Y overwrites S|K strip by strip
   const size_t slabs = (size_t)p->ctx->sms;
   if (p->work_slabs < slabs || p->work_slab_bytes < slab_per_cta) {
     if (p->work) cudaFree(p->work);
@@ -317,7 +321,7 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
     CUDA_TRY(cudaEventRecord(e0, st));
   }
-  if (big2ds_has(Ph, Pw, pl.h.radix, pl.h.nstages, pl.w.radix, pl.w.nstages)) CUDA_TRY(launch_conv_big2ds(q, grid, smem, st));
+  if (tuned) CUDA_TRY(launch_conv_big2ds(q, grid, smem, st));
   else CUDA_TRY(launch_conv_big2d(q, grid, smem, st));
   ++g_launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }

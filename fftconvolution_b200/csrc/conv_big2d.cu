@@ -36,9 +36,9 @@ __global__ void __launch_bounds__(512, 1) conv_big2d_kernel(const __grid_constan
   const int HW = p.half_w;
   const bool plain_kernel = (p.hk <= p.kwrap_h) && (p.wk <= p.kwrap_w);
   const size_t src_sz = (size_t)p.hs * p.ws, dst_sz = (size_t)p.hd * p.wd;
-  cplx* slabS = p.slab + (size_t)blockIdx.x * (size_t)(p.hs + hke + p.rows_y) * HW;
+  cplx* slabS = p.slab + (size_t)blockIdx.x * (size_t)max(p.hs + hke, p.rows_y) * HW;
   cplx* slabK = slabS + (size_t)p.hs * HW;
-  cplx* slabY = slabK + (size_t)hke * HW;
+  cplx* slabY = slabS;   // in place: a strip's Y columns replace the S and K columns it consumed
   const float inv_ldw = 1.0f / (float)p.ldw, inv_hw = 1.0f / (float)HW, inv_ldc = 1.0f / (float)p.ldc;
   const float inv_wd = 1.0f / (float)p.wd, inv_pw = 1.0f / (float)Pw;
 

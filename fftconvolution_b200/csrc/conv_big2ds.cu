@@ -2,14 +2,22 @@
 // conv_big2d.cu for the period of BASELINE config 3 (100x100 (*) 100x100 CIRCULAR_FULL -> 200 x 200,
 // per-image kernels).  Replaces fftw_circular_convolution + crop (reference convolution_fftw.h:169-284).
 //
-// Same three phases and the same L2-resident slab as conv_big2d.cu (rows -> half spectra -> column
-// strips with the product -> rows), but every radix pass is instantiated for its literal length,
-// block size and radix, and the work is laid out so that
+// Same three phases as conv_big2d.cu (rows -> half spectra -> column strips with the product -> rows)
+// through a per-CTA slab that stays in L2, with these differences:
+//   * 200 = 10 x 20: two passes per transform (prime-factor butterflies of 10 and 20 points in
+//     registers) instead of three radix-5/5/8 passes -- the transforms are bound by trips through
+//     shared memory and by barriers, not by the FP64 pipe; the spectrum order is a closed formula
+//     (no permutation table loads);
 //   * the 32 lanes of a warp walk adjacent LINES (rows of a chunk / columns of a strip) and a warp
-//     owns one butterfly index: block, offset and the R-1 twiddles are warp-uniform, the twiddles are
-//     constant-bank operands of the FP64 instructions (no registers, no loads, no index arithmetic);
-//   * the copy loops run one warp per row with lanes along the contiguous dimension, four
-//     independent loads in flight, and no integer division.
+//     owns one butterfly index: block, offset and twiddles are warp-uniform, the twiddles are
+//     constant-bank operands of the FP64 instructions;
+//   * column phase: last forward pass of a source column and of its kernel column, the pointwise
+//     product and the first backward pass are ONE pass over a block of 20 points in registers;
+//   * the slab is strip-major and in place: the block of a strip holds its S rows then its K rows,
+//     contiguous, and the strip's result Y replaces it.  A strip moves with bulk asynchronous copies
+//     (cp.async.bulk + mbarrier: the copy engine, no registers, no per-thread round trips to L2);
+//   * source / kernel reads and result writes carry evict-first hints so that the slabs
+//     (148 x 323 KB) stay resident in the 126 MB L2.
 #include "conv_params.h"
 #include "tw200_table.h"
 
@@ -29,19 +37,54 @@ __device__ long long g_acc[16];   // debug variant: cycles accumulated per phase
 #define B2C_T(slot)
 #endif
 
+// ---- bulk asynchronous copies (TMA engine, no registers, no per-thread latency) -----------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_proxy() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+template <int R> struct Rbfly { static __device__ __forceinline__ void run(cplx* v) { Rbfly<R>::run(v); } };
+template <> struct Rbfly<10> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 5>(v); } };
+template <> struct Rbfly<20> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<4, 5>(v); } };
+
 template <int P> struct TwTable;
 template <> struct TwTable<200> { static __device__ __forceinline__ cplx at(int k) { return c_tw200[k]; } };
 
 // One radix-R stage of a length-P transform on `nlines` lines (element k of line l at W[l*ls + k*es]),
 // block length N, lanes = lines, warps = butterfly indices.
 template <int P, int R, int N, bool INV>
-__device__ __forceinline__ void stage(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane) {
+__device__ __forceinline__ void stage(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane,
+                                      int nsplit = 1 << 30, int kjump = 0) {
   constexpr int M = N / R, PER_LINE = P / R, TSTEP = P / N;
-  for (int t = warp; t < PER_LINE; t += nwarps) {      // warp-uniform
+  const int ntrips = (nlines + 31) >> 5;
+  for (int task = warp; task < PER_LINE * ntrips; task += nwarps) {      // warp-uniform
+    const int t = task / ntrips, line = ((task - t * ntrips) << 5) + lane;
     const int b = t / M, j = t - b * M;
     cplx* base = W + (b * N + j) * es;
-    for (int line = lane; line < nlines; line += 32) {
-      cplx* p = base + line * ls;
+    if (line < nlines) {
+      cplx* p = base + line * ls + (line >= nsplit ? kjump : 0);   // lines past nsplit live in a second array
       cplx v[R];
 #pragma unroll
       for (int q = 0; q < R; ++q) v[q] = p[q * M * es];
@@ -52,11 +95,11 @@ __device__ __forceinline__ void stage(cplx* W, int es, int ls, int nlines, int w
         }
 #pragma unroll
         for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
-        Bfly<R>::run(v);
+        Rbfly<R>::run(v);
 #pragma unroll
         for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
       } else {
-        Bfly<R>::run(v);
+        Rbfly<R>::run(v);
         if (M > 1) {
 #pragma unroll
           for (int q = 1; q < R; ++q) v[q] = cmul(v[q], TwTable<P>::at(j * q * TSTEP));
@@ -69,16 +112,57 @@ __device__ __forceinline__ void stage(cplx* W, int es, int ls, int nlines, int w
   __syncthreads();
 }
 
-template <int P, int R0, int R1, int R2>
+// Two-pass schedule P = R0 * R1: a radix-R0 pass with twiddles, then a twiddle-free radix-R1 pass (each a
+// prime-factor butterfly in registers).  Two passes instead of three radix-5/5/8 passes: the strip
+// transforms are bound by shared-memory traffic, not by the FP64 pipe.  Frequency f ends at position
+// (f % R0) * R1 + f / R0.
+template <int P, int R0, int R1>
 struct Fft {
+  static_assert(R0 * R1 == P, "two-pass schedule");
+  static __device__ __forceinline__ int pos_of(int f) { return (f % R0) * R1 + f / R0; }
   static __device__ __forceinline__ void forward(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane) {
     stage<P, R0, P, false>(W, es, ls, nlines, warp, nwarps, lane);
-    stage<P, R1, P / R0, false>(W, es, ls, nlines, warp, nwarps, lane);
-    stage<P, R2, P / R0 / R1, false>(W, es, ls, nlines, warp, nwarps, lane);
+    stage<P, R1, R1, false>(W, es, ls, nlines, warp, nwarps, lane);
   }
   static __device__ __forceinline__ void backward(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane) {
-    stage<P, R2, P / R0 / R1, true>(W, es, ls, nlines, warp, nwarps, lane);
-    stage<P, R1, P / R0, true>(W, es, ls, nlines, warp, nwarps, lane);
+    stage<P, R1, R1, true>(W, es, ls, nlines, warp, nwarps, lane);
+    stage<P, R0, P, true>(W, es, ls, nlines, warp, nwarps, lane);
+  }
+  // Column phase, fused: (last forward pass of line l and of its partner koff elements further) ->
+  // pointwise product * scale -> first backward pass, all on one block of R1 points in registers
+  // (convolution_fftw.h:195-204, 210-211 between the two transforms).  One barrier and two trips
+  // through shared memory fewer than forward-pass / product / backward-pass.
+  static __device__ __forceinline__ void middle(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane,
+                                                int koff, double scale) {
+    const int ntrips = (nlines + 31) >> 5;
+    for (int task = warp; task < R0 * ntrips; task += nwarps) {
+      const int b = task / ntrips, line = ((task - b * ntrips) << 5) + lane;
+      if (line < nlines) {
+        cplx* ps = W + b * R1 * es + line * ls;
+        cplx k[R1], v[R1];
+#pragma unroll
+        for (int q = 0; q < R1; ++q) k[q] = ps[q * es + koff];
+        Rbfly<R1>::run(k);
+#pragma unroll
+        for (int q = 0; q < R1; ++q) v[q] = ps[q * es];
+        Rbfly<R1>::run(v);
+#pragma unroll
+        for (int q = 0; q < R1; ++q) {
+          const cplx y = cmul(v[q], k[q]);
+          v[q] = make_double2(y.y * scale, y.x * scale);   // swapped: inverse butterfly = forward on (im, re)
+        }
+        Rbfly<R1>::run(v);
+#pragma unroll
+        for (int q = 0; q < R1; ++q) ps[q * es] = cswap(v[q]);
+      }
+    }
+    __syncthreads();
+  }
+  static __device__ __forceinline__ void forward_first(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane,
+                                                       int nsplit, int kjump) {
+    stage<P, R0, P, false>(W, es, ls, nlines, warp, nwarps, lane, nsplit, kjump);
+  }
+  static __device__ __forceinline__ void backward_last(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane) {
     stage<P, R0, P, true>(W, es, ls, nlines, warp, nwarps, lane);
   }
 };
@@ -90,22 +174,34 @@ __device__ __forceinline__ double wrapped_tap(const BigParams& p, const double* 
   return acc;
 }
 
-template <int P, int R0, int R1, int R2>
-__global__ void __launch_bounds__(512, 1) conv_kernel(const __grid_constant__ BigParams p) {
-  typedef Fft<P, R0, R1, R2> F;
+template <int P, int R0, int R1, int NT>
+__global__ void __launch_bounds__(NT, 1) conv_kernel(const __grid_constant__ BigParams p) {
+  typedef Fft<P, R0, R1> F;
   cplx* W = reinterpret_cast<cplx*>(b2c_smem_bigs);
   const int lane = threadIdx.x & 31;
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // uniform for the compiler
   const int nwarps = blockDim.x >> 5;
   const int hke = min(p.hk, p.kwrap_h), wke = min(p.wk, p.kwrap_w);
   const int rows_in = max(p.hs, hke);
-  const int HW = p.half_w, ldw = p.ldw, ldc = p.ldc;
+  const int HW = p.half_w, ldw = p.ldw;
   const bool plain_kernel = (p.hk <= p.kwrap_h) && (p.wk <= p.kwrap_w);
   const size_t src_sz = (size_t)p.hs * p.ws, dst_sz = (size_t)p.hd * p.wd;
-  cplx* slabS = p.slab + (size_t)blockIdx.x * (size_t)(p.hs + hke + p.rows_y) * HW;
-  cplx* slabK = slabS + (size_t)p.hs * HW;
-  cplx* slabY = slabK + (size_t)hke * HW;
-  const int* __restrict__ posf = p.aw.posf;
+  // Per-CTA slab, strip-major: the block of strip v0 starts at rows_total * v0 and holds [hs][nc] S rows
+  // followed by [hke][nc] K rows -- one contiguous run per transfer; the strip's Y[rows_y][nc] later
+  // replaces the block in place.
+  constexpr int NQ = 1;                                      // pieces per bulk transfer (more pieces measured no faster)
+  constexpr int CS = 32;                                     // half-spectrum columns per strip
+  const int rows_total = max(p.hs + hke, p.rows_y);
+  cplx* slab = p.slab + (size_t)blockIdx.x * (size_t)rows_total * HW;
+  __shared__ unsigned long long bar_storage;
+  unsigned long long* bar = &bar_storage;
+  unsigned bar_phase = 0;
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  fence_async_proxy();
+  __syncthreads();
 
 #if B2C_BIGS_TRACE
   long long tprev; asm volatile("mov.u64 %0, %%clock64;" : "=l"(tprev));
@@ -128,8 +224,8 @@ __global__ void __launch_bounds__(512, 1) conv_kernel(const __grid_constant__ Bi
         for (int u = 0; u < NCH; ++u) {
           const int c = lane + 32 * u;
           v[u] = make_double2(0.0, 0.0);
-          if (r < p.hs && c < p.ws) v[u].x = __ldg(arow + c);
-          if (r < hke && c < wke) v[u].y = plain_kernel ? __ldg(krow + c) : wrapped_tap(p, k, r, c);
+          if (r < p.hs && c < p.ws) v[u].x = __ldcs(arow + c);          // streamed once: evict first, keep the slabs in L2
+          if (r < hke && c < wke) v[u].y = plain_kernel ? __ldcs(krow + c) : wrapped_tap(p, k, r, c);
         }
 #pragma unroll
         for (int u = 0; u < NCH; ++u)
@@ -144,62 +240,64 @@ __global__ void __launch_bounds__(512, 1) conv_kernel(const __grid_constant__ Bi
         const int r = r0 + rr;
         const cplx* wrow = W + rr * ldw;
         for (int v = lane; v < HW; v += 32) {
-          const cplx z1 = wrow[__ldg(posf + v)];
-          const cplx z2 = wrow[__ldg(posf + (v ? P - v : 0))];
-          if (r < p.hs) slabS[(size_t)r * HW + v] = make_double2(0.5 * (z1.x + z2.x), 0.5 * (z1.y - z2.y));
-          if (r < hke) slabK[(size_t)r * HW + v] = make_double2(0.5 * (z1.y + z2.y), 0.5 * (z2.x - z1.x));
+          const cplx z1 = wrow[F::pos_of(v)];
+          const cplx z2 = wrow[F::pos_of(v ? P - v : 0)];
+          const int v0 = v & ~(CS - 1), nc = min(CS, HW - v0);
+          cplx* blk = slab + (size_t)rows_total * v0 + (v - v0);
+          if (r < p.hs) blk[r * nc] = make_double2(0.5 * (z1.x + z2.x), 0.5 * (z1.y - z2.y));
+          if (r < hke) blk[(p.hs + r) * nc] = make_double2(0.5 * (z1.y + z2.y), 0.5 * (z2.x - z1.x));
         }
       }
+      __threadfence();          // slab rows must be in L2 and ordered before the copy engine reads them
+      fence_async_proxy();
       __syncthreads();
       B2C_T(2);
     }
 
     // ---------------- phase C: strips of half-spectrum columns: both column transforms, product, backward
-    for (int v0 = 0; v0 < HW; v0 += p.cols_strip) {
-      const int nc = min(p.cols_strip, HW - v0);
-      for (int rb = 4 * warp; rb < P; rb += 4 * nwarps) {     // four rows per warp trip: 8+ loads in flight per lane
-        for (int c0 = lane; c0 < 2 * nc; c0 += 64) {
-          cplx v[4][2];
-#pragma unroll
-          for (int rr = 0; rr < 4; ++rr) {
-            const int r = rb + rr;
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const int c = c0 + 32 * u;
-              v[rr][u] = make_double2(0.0, 0.0);
-              if (c < nc) { if (r < p.hs) v[rr][u] = slabS[(size_t)r * HW + v0 + c]; }
-              else if (c < 2 * nc) { if (r < hke) v[rr][u] = slabK[(size_t)r * HW + v0 + c - nc]; }
-            }
-          }
-#pragma unroll
-          for (int rr = 0; rr < 4; ++rr)
-#pragma unroll
-            for (int u = 0; u < 2; ++u)
-              if (rb + rr < P && c0 + 32 * u < 2 * nc) W[(rb + rr) * ldc + c0 + 32 * u] = v[rr][u];
-        }
+    for (int v0 = 0; v0 < HW; v0 += CS) {
+      const int nc = min(CS, HW - v0);
+      cplx* WK = W + P * nc;                                  // S columns in W[r][nc], K columns in WK[r][nc]
+      const cplx* blk = slab + (size_t)rows_total * v0;       // this strip's block: [hs][nc] S rows, then [hke][nc] K rows
+      // Two bulk asynchronous copies (the copy engine, no registers, no per-thread round trips to L2)
+      // while the threads clear the zero-padding rows.
+      if (threadIdx.x == 0) mbar_expect_tx(bar, (unsigned)((p.hs + hke) * nc * sizeof(cplx)));
+      if (threadIdx.x < 2 * NQ) {
+        const int q = threadIdx.x % NQ, isk = threadIdx.x / NQ;
+        const int rows = isk ? hke : p.hs, per = (rows + NQ - 1) / NQ, ra = min(rows, q * per), rb = min(rows, ra + per);
+        if (rb > ra)
+          bulk_g2s((isk ? WK : W) + ra * nc, blk + (size_t)((isk ? p.hs : 0) + ra) * nc, (unsigned)((rb - ra) * nc * sizeof(cplx)), bar);
       }
+      for (int i = p.hs * nc + threadIdx.x; i < P * nc; i += NT) W[i] = make_double2(0.0, 0.0);
+      for (int i = hke * nc + threadIdx.x; i < P * nc; i += NT) WK[i] = make_double2(0.0, 0.0);
+      mbar_wait(bar, bar_phase);
+      bar_phase ^= 1u;
       __syncthreads();
       B2C_T(3);
-      F::forward(W, ldc, 1, 2 * nc, warp, nwarps, lane);
+      const int kjump = P * nc - nc;                          // line nc + c is column c of WK
+      F::forward_first(W, nc, 1, 2 * nc, warp, nwarps, lane, nc, kjump);
       B2C_T(4);
-      for (int r = warp; r < P; r += nwarps) {   // product, 1/N folded in (convolution_fftw.h:195-204, 210-211)
-        cplx* wrow = W + r * ldc;
-        for (int c = lane; c < nc; c += 32) {
-          const cplx y = cmul(wrow[c], wrow[nc + c]);
-          wrow[c] = make_double2(y.x * p.scale, y.y * p.scale);
-        }
-      }
-      __syncthreads();
+      F::middle(W, nc, 1, nc, warp, nwarps, lane, P * nc, p.scale);
       B2C_T(5);
-      F::backward(W, ldc, 1, nc, warp, nwarps, lane);
+      F::backward_last(W, nc, 1, nc, warp, nwarps, lane);
       B2C_T(6);
-      for (int r = warp; r < p.rows_y; r += nwarps) {
-        const cplx* wrow = W + r * ldc;
-        for (int c = lane; c < nc; c += 32) slabY[(size_t)r * HW + v0 + c] = wrow[c];
+      fence_async_proxy();      // the strip was written by ordinary stores; the copy engine reads it next
+      __syncthreads();
+      B2C_T(11);
+      if (threadIdx.x < NQ) {   // Y[rows_y][nc] replaces the strip's S|K block
+        const int per = (p.rows_y + NQ - 1) / NQ, ra = min(p.rows_y, (int)threadIdx.x * per), rb = min(p.rows_y, ra + per);
+        if (rb > ra)
+          bulk_s2g(slab + (size_t)rows_total * v0 + (size_t)ra * nc, W + ra * nc, (unsigned)((rb - ra) * nc * sizeof(cplx)));
+        bulk_commit();
+        bulk_wait_read();       // the buffer may be reused; the write to the slab completes in the background
       }
+      B2C_T(12);
       __syncthreads();
       B2C_T(7);
     }
+    if (threadIdx.x < NQ) bulk_wait_all();   // every Y block has landed before the row phase reads it
+    __syncthreads();
+    B2C_T(13);
 
     // ---------------- phase R': W = Y_r + i*Y_{r+1} (Hermitian-extended), backward rows, crop -> dst
     double* d = p.dst + (size_t)img * dst_sz;
@@ -208,8 +306,7 @@ __global__ void __launch_bounds__(512, 1) conv_kernel(const __grid_constant__ Bi
       const int nq = min(p.rows_chunk, pairs - q0);
       for (int qq = warp; qq < nq; qq += nwarps) {
         const int i0 = 2 * (q0 + qq), i1 = i0 + 1;
-        const cplx* y0row = slabY + (size_t)(p.off_h + i0) * HW;
-        const cplx* y1row = slabY + (size_t)(p.off_h + i1) * HW;
+        const int row0 = p.off_h + i0, row1 = p.off_h + i1;
         const bool has1 = i1 < p.hd;
         cplx* wrow = W + qq * ldw;
         constexpr int NCH = (P + 31) / 32;
@@ -221,10 +318,12 @@ __global__ void __launch_bounds__(512, 1) conv_kernel(const __grid_constant__ Bi
           pos[u] = -1;
           if (v < P) {
             const int vv = v < HW ? v : P - v;
-            y0[u] = y0row[vv];
-            y1[u] = has1 ? y1row[vv] : make_double2(0.0, 0.0);
+            const int v0 = vv & ~(CS - 1), nc = min(CS, HW - v0);
+            const cplx* blk = slab + (size_t)rows_total * v0 + (vv - v0);
+            y0[u] = __ldcg(blk + row0 * nc);   // written by the copy engine: read at L2, never from a stale L1 line
+            y1[u] = has1 ? __ldcg(blk + row1 * nc) : make_double2(0.0, 0.0);
             if (v >= HW) { y0[u].y = -y0[u].y; y1[u].y = -y1[u].y; }   // Hermitian mirror
-            pos[u] = __ldg(posf + v);
+            pos[u] = F::pos_of(v);
           }
         }
 #pragma unroll
@@ -240,8 +339,8 @@ __global__ void __launch_bounds__(512, 1) conv_kernel(const __grid_constant__ Bi
         if (i < p.hd) {
           const cplx* wrow = W + (ri >> 1) * ldw + p.off_w;
           double* drow = d + (size_t)i * p.wd;
-          if (ri & 1) { for (int j = lane; j < p.wd; j += 32) drow[j] = wrow[j].y; }
-          else        { for (int j = lane; j < p.wd; j += 32) drow[j] = wrow[j].x; }
+          if (ri & 1) { for (int j = lane; j < p.wd; j += 32) __stcs(drow + j, wrow[j].y); }
+          else        { for (int j = lane; j < p.wd; j += 32) __stcs(drow + j, wrow[j].x); }
         }
       }
       __syncthreads();
@@ -258,14 +357,16 @@ extern "C" int b2c_debug_bigs_read(long long* host) { return (int)cudaMemcpyFrom
 #endif
 
 bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, int ns_w) {
-  auto is200 = [](int P, const int* r, int ns) { return P == 200 && ns == 3 && r[0] == 5 && r[1] == 5 && r[2] == 8; };
-  return is200(Ph, rad_h, ns_h) && is200(Pw, rad_w, ns_w);
+  (void)rad_h; (void)ns_h; (void)rad_w; (void)ns_w;   // the kernel carries its own radix schedule and spectrum order
+  return Ph == 200 && Pw == 200;
 }
 
+// 384 threads: the fused middle pass keeps 2 x 20 complex values per thread (168 registers)
 cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st) {
-  auto kern = bigs::conv_kernel<200, 5, 5, 8>;
+  constexpr int NT = 384;
+  auto kern = bigs::conv_kernel<200, 10, 20, NT>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  kern<<<grid, 512, smem, st>>>(p);
+  kern<<<grid, NT, smem, st>>>(p);
   return cudaGetLastError();
 }
 

@@ -57,7 +57,7 @@ struct BigParams {
   long ker_stride;   // 0: one shared kernel
   double* dst;
   long n_images;
-  cplx* slab;        // [gridDim.x][(hs + hke + rows_y) * half_w]
+  cplx* slab;        // [gridDim.x][max(hs + hke, rows_y) * half_w]: Y replaces S|K strip by strip
 };
 
 }  // namespace b2c

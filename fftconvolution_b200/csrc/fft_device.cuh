@@ -145,6 +145,39 @@ struct Bfly<8> {
   }
 };
 
+// ---- small-radix butterflies by prime-factor (Good-Thomas) composition: no internal twiddles ----
+__host__ __device__ constexpr int inv_mod(int a, int m) {
+  for (int x = 1; x < m; ++x)
+    if ((a * x) % m == 1) return x;
+  return 1;
+}
+
+// N = A * B, gcd(A, B) = 1: input n = (B*n1 + A*n2) mod N, output k = (B*B'*k1 + A*A'*k2) mod N
+template <int A, int B>
+__device__ __forceinline__ void bfly_pfa(cplx* v) {
+  constexpr int N = A * B;
+  constexpr int ea = B * inv_mod(B % A, A), eb = A * inv_mod(A % B, B);
+  cplx u[A][B];
+#pragma unroll
+  for (int n1 = 0; n1 < A; ++n1) {
+    cplx t[B];
+#pragma unroll
+    for (int n2 = 0; n2 < B; ++n2) t[n2] = v[(B * n1 + A * n2) % N];
+    Bfly<B>::run(t);
+#pragma unroll
+    for (int k2 = 0; k2 < B; ++k2) u[n1][k2] = t[k2];
+  }
+#pragma unroll
+  for (int k2 = 0; k2 < B; ++k2) {
+    cplx s[A];
+#pragma unroll
+    for (int n1 = 0; n1 < A; ++n1) s[n1] = u[n1][k2];
+    Bfly<A>::run(s);
+#pragma unroll
+    for (int k1 = 0; k1 < A; ++k1) v[(ea * k1 + eb * k2) % N] = s[k1];
+  }
+}
+
 // One radix-R stage over `nlines` independent lines living in one work buffer.
 //   element k of line l is at  W[l*ls + k*es]
 //   P    : transform length;  n : current block length (n % R == 0);  m = n / R

@@ -162,6 +162,35 @@ def test_config3_shape_and_circular_full_identity(b2c, oracle, torch_cuda):
     _check(b.convolve_host(src, ker), got, "LINEAR_FULL == CIRCULAR_FULL")
 
 
+def test_strip_mode_many_images_per_cta(b2c, oracle, torch_cuda):
+    """Strip-mode kernels are persistent: one CTA walks several images through the same slab and the
+    same shared-memory buffers.  A batch much larger than the grid, built from a few distinct
+    (source, kernel) pairs, must give every copy the bit pattern of its prototype (which is checked
+    against the oracle) -- catches stale slab / cache lines carried from one image to the next."""
+    torch = torch_cuda
+    rng = np.random.default_rng(77)
+    for (mode, hs, ws, hk, wk, n) in [(7, 100, 100, 100, 100, 2 * 148 + 41), (0, 120, 90, 70, 100, 148 + 19)]:
+        nproto = 3
+        psrc, pker = rng.random((nproto, hs, ws)), rng.random((nproto, hk, wk))
+        which = rng.integers(0, nproto, size=n)
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        assert not p.info()["work_in_smem"]
+        p.set_path(b2c.PATH_FFT)
+        d_src = torch.from_numpy(psrc[which]).cuda()
+        d_ker = torch.from_numpy(pker[which]).cuda()
+        d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+        for _ in range(2):   # second pass starts from slabs left by the first
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 0, d_dst.data_ptr(), n, 0)
+        torch.cuda.synchronize()
+        got = d_dst.cpu().numpy()
+        first = [int(np.flatnonzero(which == j)[0]) for j in range(nproto)]
+        for j in range(nproto):
+            _check(got[first[j]], oracle.convolve_direct8(mode, psrc[j], pker[j]), ("prototype", mode, j))
+        for i in range(n):
+            assert np.array_equal(got[i], got[first[which[i]]]), ("copy differs from its prototype", mode, i)
+        p.destroy()
+
+
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
     """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
     rng = np.random.default_rng(14)
