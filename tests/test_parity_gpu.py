@@ -191,6 +191,32 @@ def test_strip_mode_many_images_per_cta(b2c, oracle, torch_cuda):
         p.destroy()
 
 
+def test_strip_mode_split_form_small_batches_and_large_images(b2c, oracle, torch_cuda):
+    """Batches far from a whole number of waves run one launch per phase with one CTA per chunk / strip
+    (conv_big2d.cu split form): every crop mode, rectangles, shared and per-image kernels, batch sizes
+    across the group boundary (74 on 148 SMs), and one 1024 x 1024 image."""
+    torch = torch_cuda
+    rng = np.random.default_rng(91)
+    cases = [(0, 150, 130, 31, 60, 1, 1), (2, 170, 90, 40, 120, 5, 0), (3, 160, 170, 9, 30, 2, 1), (5, 128, 128, 64, 33, 3, 0),
+             (7, 100, 100, 100, 100, 75, 0), (2, 200, 190, 17, 17, 160, 1), (2, 1024, 1024, 33, 33, 1, 1)]
+    for (mode, hs, ws, hk, wk, n, shared) in cases:
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        assert not p.info()["work_in_smem"], (mode, hs, ws, hk, wk)
+        p.set_path(b2c.PATH_FFT)
+        src = rng.random((n, hs, ws))
+        ker = rng.random((hk, wk)) if shared else rng.random((n, hk, wk))
+        d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+        d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+        p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), shared, d_dst.data_ptr(), n, 0)
+        torch.cuda.synchronize()
+        got = d_dst.cpu().numpy()
+        for i in sorted({0, n // 2, n - 1}):
+            want = oracle.convolve_direct8(mode, src[i], ker if shared else ker[i])
+            _check(got[i], want, ("split form", mode, hs, ws, hk, wk, n, i))
+        assert np.isfinite(got).all()
+        p.destroy()
+
+
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
     """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
     rng = np.random.default_rng(14)
