@@ -160,6 +160,7 @@ struct b2c_plan {
   // (coalesced lanes), reported back in the caller's orientation
   bool transposed = false;
   int forced_path = B2C_PATH_AUTO;
+  bool strip_only = false;   // too large for the any-size kernel: B2C_PATH_FFT_GENERIC is refused
   // lazily created device state (one device per plan)
   DeviceCtx* ctx = nullptr;
   AxisTables th, tw;
@@ -545,9 +546,16 @@ int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kerne
     return fail(B2C_EINVAL, "b2c_plan_create: planning failed");
   }
   if (!p->pl.empty && (long)p->pl.h.P * (long)work_ld(p->pl) >= (1L << 24)) {
+    // Beyond the any-size kernel's 32-bit work-buffer offsets only strip mode runs (conv_big2d.cu):
+    // it needs one row and a strip of one column pair in shared memory (227 KB) and no folding.
     const int ph = p->pl.h.P, pw = p->pl.w.P;
-    delete p;
-    return fail(B2C_ESIZE, "b2c_plan_create: transform of %d x %d points exceeds the engine's work-buffer index range", ph, pw);
+    const bool strips_ok = p->pl.h.fold == 0 && p->pl.w.fold == 0 && ph <= 4800 && pw <= 14000;
+    if (strips_ok) {
+      p->strip_only = true;
+    } else {
+      delete p;
+      return fail(B2C_ESIZE, "b2c_plan_create: transform of %d x %d points exceeds the engine's work-buffer index range", ph, pw);
+    }
   }
   *plan = p;
   return 0;
@@ -581,6 +589,8 @@ int b2c_plan_info(const b2c_plan* p, int* path, int* off_h, int* off_w, int* fol
 
 int b2c_plan_set_path(b2c_plan* p, int path) {
   if (!p || path < 0 || path > 3) return fail(B2C_EINVAL, "b2c_plan_set_path: bad arguments");
+  if (path == B2C_PATH_FFT_GENERIC && p->strip_only)
+    return fail(B2C_ESIZE, "b2c_plan_set_path: a transform this large only runs in strip mode");
   p->forced_path = path;
   return 0;
 }

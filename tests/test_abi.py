@@ -124,3 +124,21 @@ def test_partition_covers_batch(b2c):
             assert all(e - b <= per for b, e in spans)
     with pytest.raises(b2c.B2CError):
         b2c.partition(10, 2, 2)
+
+
+def test_size_limits_of_planning(b2c):
+    """Planning is host-only: transforms past the any-size kernel's index range are accepted when strip
+    mode can run them (no folding, period <= 4800 rows) and refuse the generic path; others fail with
+    B2C_ESIZE and a message."""
+    p = b2c.Plan(b2c.LINEAR_SAME, 4096, 4096, 15, 15)
+    assert (p.h_dst, p.w_dst) == (4096, 4096) and p.h_fft >= 4103
+    with pytest.raises(b2c.B2CError) as e:
+        p.set_path(b2c.PATH_FFT_GENERIC)
+    assert e.value.code == 4 and "strip mode" in str(e.value)
+    p.destroy()
+    with pytest.raises(b2c.B2CError) as e:
+        b2c.Plan(b2c.CIRCULAR_SAME, 4099, 4099, 3, 3)      # prime size: fold path only
+    assert e.value.code == 4
+    with pytest.raises(b2c.B2CError) as e:
+        b2c.Plan(b2c.LINEAR_FULL, 6000, 6000, 3, 3)
+    assert e.value.code == 4

@@ -194,11 +194,12 @@ def test_strip_mode_many_images_per_cta(b2c, oracle, torch_cuda):
 def test_strip_mode_split_form_small_batches_and_large_images(b2c, oracle, torch_cuda):
     """Batches far from a whole number of waves run one launch per phase with one CTA per chunk / strip
     (conv_big2d.cu split form): every crop mode, rectangles, shared and per-image kernels, batch sizes
-    across the group boundary (74 on 148 SMs), and one 1024 x 1024 image."""
+    across the group boundary (74 on 148 SMs), one 1024 x 1024 and one 4096 x 4096 image."""
     torch = torch_cuda
     rng = np.random.default_rng(91)
     cases = [(0, 150, 130, 31, 60, 1, 1), (2, 170, 90, 40, 120, 5, 0), (3, 160, 170, 9, 30, 2, 1), (5, 128, 128, 64, 33, 3, 0),
-             (7, 100, 100, 100, 100, 75, 0), (2, 200, 190, 17, 17, 160, 1), (2, 1024, 1024, 33, 33, 1, 1)]
+             (7, 100, 100, 100, 100, 75, 0), (2, 200, 190, 17, 17, 160, 1), (2, 1024, 1024, 33, 33, 1, 1),
+             (2, 4096, 4096, 5, 5, 1, 1)]   # last: beyond the any-size kernel's index range, strip mode only
     for (mode, hs, ws, hk, wk, n, shared) in cases:
         p = b2c.Plan(mode, hs, ws, hk, wk)
         assert not p.info()["work_in_smem"], (mode, hs, ws, hk, wk)

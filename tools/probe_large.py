@@ -5,9 +5,9 @@ import numpy as np, torch, fftconvolution_b200 as b2c
 from scipy.signal import fftconvolve
 torch.cuda.set_device(0)
 rng = np.random.default_rng(5)
-for (hs, hk, n) in [(160, 31, 296), (256, 31, 296), (384, 31, 296), (512, 31, 296), (1024, 63, 160)]:
+for (hs, hk, n) in [(4096, 15, 1), (4096, 63, 2), (4500, 129, 1)]:
     try:
-        p = b2c.Plan(b2c.LINEAR_SAME, hs, hs, hk, hk)
+        p = b2c.Plan(b2c.LINEAR_SAME, hs, hs, hk, hk); p.set_path(b2c.PATH_FFT)
         info = p.info()
         src = rng.random((n, hs, hs)); ker = rng.random((hk, hk))
         d_src = torch.from_numpy(src).cuda(); d_ker = torch.from_numpy(ker).cuda()
