@@ -188,11 +188,34 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit_line(line)
     return 0
 
 
 # ------------------------------------------------------------------------------------------------
+def pin_to_gpu_numa_node(torch, local_rank):
+    """Bind this rank's host threads (and, by first touch, its pinned staging buffers) to the NUMA node
+    its GPU hangs off -- otherwise the end-to-end leg of N ranks fights over one socket's memory.
+    Best effort: returns a description for the JSON line, or None when the topology cannot be read."""
+    try:
+        pr = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "cpus": len(cpus)}
+    except Exception:
+        return None
+
+
 def run_b2c_arm(args):
     import numpy as np
     import torch
@@ -205,6 +228,7 @@ def run_b2c_arm(args):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the engine has no CPU fallback")
+    pinned = pin_to_gpu_numa_node(torch, local_rank) if (world > 1 and not os.environ.get("B2C_BENCH_NO_PIN")) else None
     torch.cuda.set_device(local_rank)
     b2c.lib().b2c_set_device(local_rank)
     if world > 1:
@@ -292,7 +316,7 @@ def run_b2c_arm(args):
         ok = bool(torch.equal(h_dst[:64], d_dst[:64].cpu()))
         e2e = {"value": n_e2e * world * e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": src_bytes + HK * WK * 8,
                "d2h_bytes_per_step": dst_bytes, "batch_per_gpu": n_e2e, "steps": e_steps,
-               "matches_device_path": ok}
+               "matches_device_path": ok, "host_affinity": pinned}
         del h_src, h_dst
     except Exception as ex:  # pinned allocation can fail on a small host; say so instead of faking a number
         e2e = {"value": None, "unit": UNIT, "error": str(ex)[:200]}
@@ -336,10 +360,28 @@ def run_b2c_arm(args):
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": sampler.result(), "checksum_sum63": int(cs_t.item()),
         }
-        print(json.dumps(line))
+        emit_line(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout, but libraries write there too (NCCL prints its version
+    banner on stdout).  Keep a private handle on the real stdout for the result line and point fd 1 at
+    stderr for everything else."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_RESULT_FD if _RESULT_FD is not None else 1, data)
 
 
 def main():
@@ -353,6 +395,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
     args = ap.parse_args()
+    claim_stdout()
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_b2c_arm(args)
