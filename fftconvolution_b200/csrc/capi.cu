@@ -26,7 +26,7 @@ cudaError_t launch_conv_perimage(const ConvParams& p, int grid, int threads, siz
 int occupancy_conv_shared(int threads, size_t smem, bool in_smem);
 int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 // conv_direct.cu
-size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out);
+size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int group = 1);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
 int occupancy_direct(int hk, int hd, size_t smem);
 // conv_big2d.cu
@@ -192,16 +192,18 @@ size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (si
 // Crossover between the direct kernel and the FFT chain: two time models per image, fitted to the
 // measured sweep profiles/r01_crossover.csv (tools/crossover_sweep.py).
 //   direct: max(HBM stream at 3.0 TB/s, FMAs at 5.8 TFMA/s) for the 8-rows-per-thread variant,
-//           HBM at 2.5 TB/s + FMAs at 3.1 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image;
+//           HBM at 2.5 TB/s + FMAs at 3.1 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image
+//           (0.4 ns with a shared kernel: small images are processed in groups per CTA);
 //           kernels taller than 16 rows run a general variant that is about 4x slower.
-//   FFT   : planner cost units x 0.15 ps, never below 8 ns per image (generic kernel); 6.5 ps per point
+//   FFT   : planner cost units x 0.15 ps, never below 10 ns per image (generic kernel); 6.5 ps per point
 //           of the period + 3 ns for the tuned square-period kernels.
 int auto_path(const Plan2D& pl, bool shared) {
   const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
   const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
   double t_direct;
-  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / 3.0e12, fma / 5.8e12) + 4e-9;
-  else t_direct = bytes / 2.5e12 + fma / 3.1e12 + 4e-9;
+  const double per_image = shared ? 0.4e-9 : 4e-9;
+  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / 3.0e12, fma / 5.8e12) + per_image;
+  else t_direct = bytes / 2.5e12 + fma / 3.1e12 + per_image;
   if (pl.h.n_ker > 16) t_direct *= 4.0;
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
@@ -210,7 +212,7 @@ int auto_path(const Plan2D& pl, bool shared) {
                      pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
   // tuned kernels: 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 3 ns
   const double pp = (double)pl.h.P * pl.w.P;
-  const double t_fft = tuned ? 6.5e-12 * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 3e-9 : std::max(8e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
+  const double t_fft = tuned ? 6.5e-12 * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 3e-9 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
   int spw;
   if (direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, std::min(8, pl.h.n_dst), &spw) > 200 * 1024) return B2C_PATH_FFT;
@@ -458,11 +460,21 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
     return fail(B2C_ESIZE, "direct kernel: %dx%d kernel does not fit in shared memory", q.hk, q.wk);
   q.tile_h = tile;
   q.tiles_per_image = (q.hd + tile - 1) / tile;
-  const size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw);
+  // Small images with a shared kernel: a CTA takes `group` whole images at a time, enough for about three
+  // tasks per thread, within 56 KB of shared memory (four CTAs per SM).
+  q.group = 1;
+  if (shared && q.tiles_per_image == 1) {
+    const int ti = q.hd >= 8 ? 8 : 1;
+    const long tasks = (long)((q.hd + ti - 1) / ti) * q.wd;
+    long g = std::min<long>(n, (768 + tasks - 1) / tasks);
+    while (g > 1 && direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw, (int)g) > 56 * 1024) --g;
+    q.group = (int)std::max<long>(1, g);
+  }
+  const size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw, q.group);
   q.sp_w = spw;
   int occ = occupancy_direct(q.hk, q.hd, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
-  const long total = n * q.tiles_per_image;
+  const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);
   if (grid < 1) grid = 1;
   cudaEvent_t e0 = nullptr, e1 = nullptr;

@@ -34,17 +34,22 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
   double* S = kflip + (size_t)p.wk * hk_pad;
   const int pitch = p.sp_w;
   const size_t src_sz = (size_t)p.hs * p.ws, ker_sz = (size_t)p.hk * p.wk, dst_sz = (size_t)p.hd * p.wd;
-  const long total = p.n_images * p.tiles_per_image;
+  // A work unit is one row tile of one image, or -- for small images with a shared kernel -- the whole
+  // of `group` consecutive images (their pixels are contiguous in memory: coalesced staging and stores,
+  // and enough tasks for all 256 threads).
+  const int group = p.group;
+  const long units = group > 1 ? (p.n_images + group - 1) / group : p.n_images * p.tiles_per_image;
   bool kernel_loaded = false;
 
-  for (long work = blockIdx.x; work < total; work += gridDim.x) {
-    const long img = work / p.tiles_per_image;
-    const int tile = (int)(work - img * p.tiles_per_image);
+  for (long work = blockIdx.x; work < units; work += gridDim.x) {
+    const long img0 = group > 1 ? work * group : work / p.tiles_per_image;
+    const int ng = group > 1 ? (int)min((long)group, p.n_images - img0) : 1;
+    const int tile = group > 1 ? 0 : (int)(work - img0 * p.tiles_per_image);
     const int i0 = tile * p.tile_h;
     const int th = min(p.tile_h, p.hd - i0);
     __syncthreads();  // previous iteration's readers are done
     if (!(p.kernel_is_shared && kernel_loaded)) {
-      const double* k = p.ker + (p.kernel_is_shared ? 0 : (size_t)img * ker_sz);
+      const double* k = p.ker + (p.kernel_is_shared ? 0 : (size_t)img0 * ker_sz);
       for (int idx = threadIdx.x; idx < p.wk * hk_pad; idx += kDirectThreads) {
         const int c = idx / hk_pad, r = idx - c * hk_pad;
         kflip[idx] = r < hk ? __ldg(&k[(size_t)(hk - 1 - r) * p.wk + (p.wk - 1 - c)]) : 0.0;
@@ -53,44 +58,51 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
     }
     // stage source rows [i0 + off_h - (hk-1), ...) with halo.  Eight independent global loads are in
     // flight per thread before the first shared store (the staging loop is latency-, not bandwidth-bound).
-    const double* a = p.src + (size_t)img * src_sz;
+    const double* a = p.src + (size_t)img0 * src_sz;
     const int rows = th + hk - 1;
     const int cols = p.wd + p.wk - 1;
-    const int nelem = rows * pitch;
-    const float inv_pitch = 1.0f / (float)pitch;
+    const int nelem = rows * pitch;            // staged doubles per image
+    const int nall = ng * nelem;
+    const float inv_pitch = 1.0f / (float)pitch, inv_nelem = 1.0f / (float)nelem;
     constexpr int SU = 8;
-    for (int base = threadIdx.x; base < nelem; base += SU * kDirectThreads) {
+    for (int base = threadIdx.x; base < nall; base += SU * kDirectThreads) {
       double vals[SU];
 #pragma unroll
       for (int k = 0; k < SU; ++k) {
         const int idx = base + k * kDirectThreads;
         double val = 0.0;
-        if (idx < nelem) {
-          const int u = fast_div(idx, pitch, inv_pitch), v = idx - u * pitch;
+        if (idx < nall) {
+          const int g = group > 1 ? fast_div(idx, nelem, inv_nelem) : 0;
+          const int rem = idx - g * nelem;
+          const int u = fast_div(rem, pitch, inv_pitch), v = rem - u * pitch;
           int sr = i0 + u + p.off_h - (hk - 1);
           int sc = v + p.off_w - (p.wk - 1);
           if (p.wrap_h) sr = wrap_index(sr, p.wrap_h);
           if (p.wrap_w) sc = wrap_index(sc, p.wrap_w);
-          if (v < cols && sr >= 0 && sr < p.hs && sc >= 0 && sc < p.ws) val = __ldg(a + (size_t)sr * p.ws + sc);
+          if (v < cols && sr >= 0 && sr < p.hs && sc >= 0 && sc < p.ws) val = __ldg(a + (size_t)g * src_sz + (size_t)sr * p.ws + sc);
         }
         vals[k] = val;
       }
 #pragma unroll
       for (int k = 0; k < SU; ++k) {
         const int idx = base + k * kDirectThreads;
-        if (idx < nelem) S[idx] = vals[k];
+        if (idx < nall) S[idx] = vals[k];
       }
     }
     __syncthreads();
-    double* d = p.dst + (size_t)img * dst_sz;
+    double* d = p.dst + (size_t)img0 * dst_sz;
     const int blocks = (th + TI - 1) / TI;
-    for (int task = threadIdx.x; task < blocks * p.wd; task += kDirectThreads) {
-      const int b = task / p.wd, j = task - b * p.wd;   // adjacent lanes -> adjacent columns
+    const int per_image = blocks * p.wd;
+    const float inv_per_image = 1.0f / (float)per_image, inv_wd = 1.0f / (float)p.wd;
+    for (int task = threadIdx.x; task < ng * per_image; task += kDirectThreads) {
+      const int g = group > 1 ? fast_div(task, per_image, inv_per_image) : 0;
+      const int t2 = task - g * per_image;
+      const int b = fast_div(t2, p.wd, inv_wd), j = t2 - b * p.wd;   // adjacent lanes -> adjacent columns
       const int r0 = b * TI;
       double acc[TI];
 #pragma unroll
       for (int t = 0; t < TI; ++t) acc[t] = 0.0;
-      const double* col = S + (size_t)r0 * pitch + j;
+      const double* col = S + (size_t)g * nelem + (size_t)r0 * pitch + j;
       if (HK > 0) {
         // rows beyond the tile's halo are never read for outputs that exist: clamp the window
         const int last = rows - 1 - r0;   // highest valid window index
@@ -118,7 +130,7 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
           }
         }
       }
-      double* o = d + (size_t)(i0 + r0) * p.wd + j;
+      double* o = d + (size_t)g * dst_sz + (size_t)(i0 + r0) * p.wd + j;
 #pragma unroll
       for (int t = 0; t < TI; ++t)
         if (r0 + t < th) o[(size_t)t * p.wd] = acc[t];
@@ -128,12 +140,12 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
 
 // Shared memory the direct kernel needs for a given row tile; the staged row pitch is returned
 // through *sp_w_out.
-size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out) {
+size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int group) {
   const int hk_pad = (hk + 1) & ~1;
   int pitch = wd + wk - 1;
   pitch = (pitch + 1) & ~1;
   if (sp_w_out) *sp_w_out = pitch;
-  return sizeof(double) * ((size_t)wk * hk_pad + (size_t)(tile_h + hk - 1) * pitch);
+  return sizeof(double) * ((size_t)wk * hk_pad + (size_t)group * (tile_h + hk - 1) * pitch);
 }
 
 typedef void (*direct_fn)(const DirectParams);

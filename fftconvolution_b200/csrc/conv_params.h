@@ -31,6 +31,7 @@ struct DirectParams {
   int wrap_h, wrap_w;    // >0: source indices wrap modulo this (CIRCULAR_SAME), else zero outside
   int tile_h;            // output rows per CTA
   int tiles_per_image;
+  int group;             // > 1: a work unit is `group` whole consecutive images (tiles_per_image == 1, shared kernel)
   int sp_w;              // padded staged-source row length (doubles)
   int kernel_is_shared;
   const double* src;
