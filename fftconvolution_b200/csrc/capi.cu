@@ -35,6 +35,9 @@ cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_
 // conv_big2ds.cu
 bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, int ns_w);
 cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st);
+bool tuned1d_has(int P);
+cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, const double* d_src, const double* d_ker,
+                           double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
 // conv_tuned108.cu
 size_t tuned108_smem_bytes();
 size_t tuned108_kspec_bytes();
@@ -196,7 +199,7 @@ size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (si
 //           (0.4 ns with a shared kernel: small images are processed in groups per CTA);
 //           kernels taller than 16 rows run a general variant that is about 4x slower.
 //   FFT   : planner cost units x 0.15 ps, never below 10 ns per image (generic kernel); 6.5 ps per point
-//           of the period + 3 ns for the tuned square-period kernels.
+//           of the period + 3 ns for the tuned square-period kernels; 9.5 ps per point for the tuned 1-D kernels.
 int auto_path(const Plan2D& pl, bool shared) {
   const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
   const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
@@ -212,7 +215,12 @@ int auto_path(const Plan2D& pl, bool shared) {
                      pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
   // tuned kernels: 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 3 ns
   const double pp = (double)pl.h.P * pl.w.P;
-  const double t_fft = tuned ? 6.5e-12 * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 3e-9 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
+  // tuned 1-D kernels (conv_tuned1d.cu): 9.5 ps per point of the period
+  const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
+                      pl.w.fold == 0 && pl.w.kwrap == pl.w.P && pl.w.n_ker <= pl.w.P;
+  const double t_fft = tuned    ? 6.5e-12 * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 3e-9
+                       : tuned1 ? 9.5e-12 * pl.w.P + 0.5e-9
+                                : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
   int spw;
   if (direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, std::min(8, pl.h.n_dst), &spw) > 200 * 1024) return B2C_PATH_FFT;
@@ -383,12 +391,37 @@ int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_
   return 0;
 }
 
+// 1-D signals (vertical period 1) with a shared kernel and a horizontal period from the 1-D menu
+// (conv_tuned1d.cu).
+bool tuned1d_applies(const b2c_plan* p, int shared) {
+  const Plan2D& pl = p->pl;
+  return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 &&
+         tuned1d_has(pl.w.P) && pl.w.fold == 0 && pl.w.kwrap == pl.w.P && pl.w.n_ker <= pl.w.P;
+}
+
+int run_tuned1d(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
+  const Plan2D& pl = p->pl;
+  if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, std::max(work_bytes(pl), sizeof(cplx) * (size_t)pl.w.P)));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_timer.on && g_timer.ev.size() < 8192) {
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, st));
+  }
+  int launches = 0;
+  CUDA_TRY(launch_tuned1d(pl.w.P, pl.w.n_src, pl.w.n_ker, pl.w.n_dst, pl.w.off, d_src, d_ker, d_dst, n, p->kspec,
+                          p->tw.tw, p->ctx->sms, st, &launches));
+  g_launches += launches;
+  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  return 0;
+}
+
 int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst,
                  long n, cudaStream_t st) {
   if (int rc = ensure_device_state(p)) return rc;
   const Plan2D& pl = p->pl;
   if (tuned108_applies(p, shared)) return run_tuned108(p, d_src, d_ker, d_dst, n, st);
   if (tuned2_applies(p, shared)) return run_tuned2(p, d_src, d_ker, d_dst, n, st);
+  if (tuned1d_applies(p, shared)) return run_tuned1d(p, d_src, d_ker, d_dst, n, st);
   if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&
       p->forced_path != B2C_PATH_FFT_GENERIC)
     return run_big2d(p, d_src, d_ker, shared, d_dst, n, st);

@@ -65,9 +65,7 @@ __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wa
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_proxy() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
-template <int R> struct Rbfly { static __device__ __forceinline__ void run(cplx* v) { Rbfly<R>::run(v); } };
-template <> struct Rbfly<10> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 5>(v); } };
-template <> struct Rbfly<20> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<4, 5>(v); } };
+template <int R> using Rbfly = BigBfly<R>;
 
 template <int P> struct TwTable;
 template <> struct TwTable<200> { static __device__ __forceinline__ cplx at(int k) { return c_tw200[k]; } };

@@ -1,0 +1,236 @@
+// Tuned fused FFT convolution for 1-D signals (1 x N rows; N x 1 columns are planned as rows) with a
+// shared kernel -- the long-kernel half of BASELINE config 4, where the direct kernel loses.
+// Replaces fftw_circular_convolution + crop (reference convolution_fftw.h:169-284) for plans whose
+// horizontal period is on the menu below and whose vertical period is 1.
+//
+// One CTA transforms TWO signals at a time as one complex sequence z = a + i*b (the convolution is
+// linear, so Re/Im of the result are the two convolutions).  The period P = R0*R1*R2(*R3) is a
+// compile-time radix schedule of big butterflies (8..20 points in registers), one butterfly per
+// thread and pass, in place in one shared buffer:
+//   pass 0      : global -> registers (zero padding in registers, coalesced) -> butterfly -> shared
+//   passes 1..  : shared -> butterfly -> shared
+//   last pass   : forward butterfly, * cached kernel spectrum (1/P folded in), backward butterfly
+//   ... mirrored backward passes; the last one crops and writes both signals to global.
+// 2*S - 1 trips through shared memory for S passes (the any-size kernel needs 2*S' + 1 with S' = 5
+// radix-3/8 passes at P = 4608, most of its instructions index arithmetic).  Forward passes are
+// decimation in frequency, backward passes the mirrored decimation in time: the spectrum stays in
+// scrambled order and the kernel spectrum is produced in the same order by the same forward code.
+// Positions are padded by one slot per LAST-radix block so that the last pass (a thread owns a
+// contiguous block) is free of bank conflicts.
+#include "conv_params.h"
+
+namespace b2c {
+
+extern __shared__ __align__(16) unsigned char b2c_smem_t1[];
+
+namespace t1 {
+
+struct Params {
+  int ns, nd, off;          // signal length, result length, crop offset
+  const double* src;        // [n][ns]
+  double* dst;              // [n][nd]
+  long n_signals;
+  const cplx* kspec;        // [P], scrambled order, scaled by 1/P
+  const cplx* tw;           // exp(-2 pi i k / P)
+};
+
+template <int P, int R0, int R1, int R2, int R3>
+struct Geo {
+  static_assert(R0 * R1 * R2 * R3 == P, "radix schedule");
+  static constexpr int NS = R3 > 1 ? 4 : 3;
+  static constexpr int LAST = R3 > 1 ? R3 : R2;
+  static constexpr int cmax(int a, int b) { return a > b ? a : b; }
+  static constexpr int cmin(int a, int b) { return a < b ? a : b; }
+  static constexpr int RMIN = cmin(cmin(R0, R1), cmin(R2, R3 > 1 ? R3 : R2));
+  static constexpr int TASKS_MAX = P / RMIN;
+  // one task per thread in the widest pass when that fits in 512 threads, else two rounds
+  static constexpr int THREADS = TASKS_MAX <= 512 ? (TASKS_MAX + 31) / 32 * 32 : (TASKS_MAX / 2 + 31) / 32 * 32;
+  static constexpr int SLOTS = P + P / LAST;
+  static constexpr size_t smem_bytes = sizeof(cplx) * (size_t)SLOTS;
+  static __host__ __device__ constexpr int pad(int p) { return p + p / LAST; }
+  static constexpr int MIN_CTAS = 2 * smem_bytes <= 225 * 1024 ? 2 : 1;   // register budget follows the CTAs that fit
+};
+
+// One pass.  N: block length of this pass, R: radix, M = N / R.  Element q of butterfly (b, j) sits
+// at position b*N + j + M*q; twiddle of output q (forward) / input q (backward) is w_N^(j*q).
+//   SRC_GLOBAL : inputs come from the two signals in global memory (first forward pass)
+//   DST_GLOBAL : outputs go to the two results in global memory, cropped (last backward pass)
+//   MULK       : M == 1: forward butterfly, multiply by the kernel spectrum, backward butterfly
+template <class G, int P, int N, int R, bool INV, bool SRC_GLOBAL, bool DST_GLOBAL, bool MULK>
+__device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, const double* b2, double* da, double* db) {
+  constexpr int M = N / R, TSTEP = P / N;
+  for (int task = threadIdx.x; task < P / R; task += G::THREADS) {
+    const int blk = task / M, j = task - blk * M;
+    const int base = blk * N + j;
+    cplx v[R];
+    if (SRC_GLOBAL) {
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        const int pos = base + M * q;
+        v[q] = make_double2(0.0, 0.0);
+        if (pos < p.ns) {
+          v[q].x = __ldg(a + pos);
+          if (b2) v[q].y = __ldg(b2 + pos);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < R; ++q) v[q] = W[G::pad(base + M * q)];
+    }
+    if (MULK) {
+      BigBfly<R>::run(v);
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        const cplx y = cmul(v[q], __ldg(p.kspec + base + q));
+        v[q] = make_double2(y.y, y.x);          // swapped: backward butterfly = forward on (im, re)
+      }
+      BigBfly<R>::run(v);
+#pragma unroll
+      for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
+    } else if (INV) {
+      if (M > 1) {
+#pragma unroll
+        for (int q = 1; q < R; ++q) v[q] = cmulc(v[q], __ldg(p.tw + j * q * TSTEP));
+      }
+#pragma unroll
+      for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
+      BigBfly<R>::run(v);
+#pragma unroll
+      for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
+    } else {
+      BigBfly<R>::run(v);
+      if (M > 1) {
+#pragma unroll
+        for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(p.tw + j * q * TSTEP));
+      }
+    }
+    if (DST_GLOBAL) {
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        const int d = base + M * q - p.off;
+        if (d >= 0 && d < p.nd) {
+          da[d] = v[q].x;
+          if (db) db[d] = v[q].y;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < R; ++q) W[G::pad(base + M * q)] = v[q];
+    }
+  }
+}
+
+template <int P, int R0, int R1, int R2, int R3>
+__device__ __forceinline__ void forward_all_but_last(cplx* W, const Params& p, const double* a, const double* b2) {
+  typedef Geo<P, R0, R1, R2, R3> G;
+  pass<G, P, P, R0, false, true, false, false>(W, p, a, b2, nullptr, nullptr);
+  __syncthreads();
+  if (G::NS == 4) {
+    pass<G, P, P / R0, R1, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    __syncthreads();
+    pass<G, P, P / R0 / R1, R2, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    __syncthreads();
+  } else {
+    pass<G, P, P / R0, R1, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    __syncthreads();
+  }
+}
+
+template <int P, int R0, int R1, int R2, int R3>
+__global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0, R1, R2, R3>::MIN_CTAS)) conv_kernel(const __grid_constant__ Params p) {
+  typedef Geo<P, R0, R1, R2, R3> G;
+  cplx* W = reinterpret_cast<cplx*>(b2c_smem_t1);
+  const long pairs = (p.n_signals + 1) / 2;
+  for (long pr = blockIdx.x; pr < pairs; pr += gridDim.x) {
+    const double* a = p.src + (size_t)(2 * pr) * p.ns;
+    const bool two = 2 * pr + 1 < p.n_signals;
+    const double* b2 = two ? a + p.ns : nullptr;
+    double* da = p.dst + (size_t)(2 * pr) * p.nd;
+    double* db = two ? da + p.nd : nullptr;
+    forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2);
+    pass<G, P, G::LAST, G::LAST, false, false, false, true>(W, p, nullptr, nullptr, nullptr, nullptr);
+    __syncthreads();
+    if (G::NS == 4) {
+      pass<G, P, P / R0 / R1, R2, true, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+      __syncthreads();
+    }
+    pass<G, P, P / R0, R1, true, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    __syncthreads();
+    pass<G, P, P, R0, true, false, true, false>(W, p, nullptr, nullptr, da, db);
+    __syncthreads();   // the next pair's first pass overwrites W
+  }
+}
+
+// Kernel spectrum in the scrambled order the product pass reads, scaled by 1/P: the same forward
+// passes applied to the zero-padded taps (one CTA, once per batch; the reference recomputes the
+// kernel transform for every signal, convolution_fftw.h:191).
+template <int P, int R0, int R1, int R2, int R3>
+__global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), 1) kspec_kernel(const __grid_constant__ Params p, cplx* out) {
+  typedef Geo<P, R0, R1, R2, R3> G;
+  cplx* W = reinterpret_cast<cplx*>(b2c_smem_t1);
+  forward_all_but_last<P, R0, R1, R2, R3>(W, p, p.src, nullptr);
+  pass<G, P, G::LAST, G::LAST, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+  __syncthreads();
+  const double scale = 1.0 / (double)P;
+  for (int i = threadIdx.x; i < P; i += G::THREADS) {
+    const cplx v = W[G::pad(i)];
+    out[i] = make_double2(v.x * scale, v.y * scale);
+  }
+}
+
+template <int P, int R0, int R1, int R2, int R3>
+cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int sms, cudaStream_t st, int* launches) {
+  typedef Geo<P, R0, R1, R2, R3> G;
+  auto kk = kspec_kernel<P, R0, R1, R2, R3>;
+  auto ck = conv_kernel<P, R0, R1, R2, R3>;
+  cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
+  cudaFuncSetAttribute(ck, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
+  Params pk = p;
+  pk.src = d_ker; pk.ns = nk; pk.n_signals = 1;
+  kk<<<1, G::THREADS, G::smem_bytes, st>>>(pk, kspec);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  ++*launches;
+  int occ = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ck, G::THREADS, G::smem_bytes);
+  if (occ < 1) return cudaErrorLaunchOutOfResources;
+  const long pairs = (p.n_signals + 1) / 2;
+  long grid = (long)sms * occ;
+  if (grid > pairs) grid = pairs;
+  ck<<<(int)grid, G::THREADS, G::smem_bytes, st>>>(p);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+}  // namespace t1
+
+// ---- the menu: (P, R0, R1, R2, R3); the planner prefers these periods for 1-D signals ------------
+#define B2C_T1_MENU(X)                                                                                          \
+  X(512, 8, 8, 8, 1) X(640, 8, 8, 10, 1) X(768, 8, 8, 12, 1) X(1024, 8, 8, 16, 1) X(1280, 8, 10, 16, 1)         \
+  X(1536, 8, 12, 16, 1) X(2048, 8, 16, 16, 1) X(2304, 9, 16, 16, 1) X(2560, 10, 16, 16, 1) X(3072, 12, 16, 16, 1) \
+  X(4096, 16, 16, 16, 1) X(4608, 18, 16, 16, 1) X(5120, 20, 16, 16, 1) X(6144, 8, 8, 8, 12) X(8192, 8, 8, 8, 16)
+
+bool tuned1d_has(int P) {
+  switch (P) {
+#define X(p, a, b, c, d) case p:
+    B2C_T1_MENU(X)
+#undef X
+    return true;
+  }
+  return false;
+}
+
+// kernel spectrum + convolution for a 1-D period P from the menu; *launches += 2
+cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, const double* d_src, const double* d_ker,
+                           double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches) {
+  t1::Params p;
+  p.ns = ns; p.nd = nd; p.off = off; p.src = d_src; p.dst = d_dst; p.n_signals = n; p.kspec = kspec; p.tw = tw;
+  switch (P) {
+#define X(pp, a, b, c, d) case pp: return t1::run<pp, a, b, c, d>(p, d_ker, nk, kspec, sms, st, launches);
+    B2C_T1_MENU(X)
+#undef X
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace b2c

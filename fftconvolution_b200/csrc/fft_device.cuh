@@ -145,6 +145,11 @@ struct Bfly<8> {
   }
 };
 
+// Forward DFT of R points in registers for every radix the tuned kernels use: the plain butterflies above,
+// prime-factor compositions of them (6, 10, 12, 14, 18, 20) and Cooley-Tukey 3x3 / 4x4 (9, 16).
+template <int R>
+struct BigBfly { static __device__ __forceinline__ void run(cplx* v) { Bfly<R>::run(v); } };
+
 // ---- small-radix butterflies by prime-factor (Good-Thomas) composition: no internal twiddles ----
 __host__ __device__ constexpr int inv_mod(int a, int m) {
   for (int x = 1; x < m; ++x)
@@ -163,7 +168,7 @@ __device__ __forceinline__ void bfly_pfa(cplx* v) {
     cplx t[B];
 #pragma unroll
     for (int n2 = 0; n2 < B; ++n2) t[n2] = v[(B * n1 + A * n2) % N];
-    Bfly<B>::run(t);
+    BigBfly<B>::run(t);
 #pragma unroll
     for (int k2 = 0; k2 < B; ++k2) u[n1][k2] = t[k2];
   }
@@ -172,11 +177,64 @@ __device__ __forceinline__ void bfly_pfa(cplx* v) {
     cplx s[A];
 #pragma unroll
     for (int n1 = 0; n1 < A; ++n1) s[n1] = u[n1][k2];
-    Bfly<A>::run(s);
+    BigBfly<A>::run(s);
 #pragma unroll
     for (int k1 = 0; k1 < A; ++k1) v[(ea * k1 + eb * k2) % N] = s[k1];
   }
 }
+
+template <> struct BigBfly<6> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 3>(v); } };
+template <> struct BigBfly<10> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 5>(v); } };
+template <> struct BigBfly<12> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<3, 4>(v); } };
+template <> struct BigBfly<14> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 7>(v); } };
+template <> struct BigBfly<9> {
+  static __device__ __forceinline__ void run(cplx* v) {
+    const cplx w1 = make_double2(0.76604444311897803520, -0.64278760968653932632);
+    const cplx w2 = make_double2(0.17364817766693034885, -0.98480775301220805937);
+    const cplx w4 = make_double2(-0.93969262078590838405, -0.34202014332566873304);
+    cplx a0[3] = {v[0], v[3], v[6]};
+    cplx a1[3] = {v[1], v[4], v[7]};
+    cplx a2[3] = {v[2], v[5], v[8]};
+    Bfly<3>::run(a0); Bfly<3>::run(a1); Bfly<3>::run(a2);
+    a1[1] = cmul(a1[1], w1); a1[2] = cmul(a1[2], w2);
+    a2[1] = cmul(a2[1], w2); a2[2] = cmul(a2[2], w4);
+#pragma unroll
+    for (int k1 = 0; k1 < 3; ++k1) {
+      cplx s[3] = {a0[k1], a1[k1], a2[k1]};
+      Bfly<3>::run(s);
+      v[k1] = s[0]; v[k1 + 3] = s[1]; v[k1 + 6] = s[2];
+    }
+  }
+};
+template <> struct BigBfly<16> {   // 4 x 4 Cooley-Tukey, twiddles w16^(n1*k2)
+  static __device__ __forceinline__ void run(cplx* v) {
+    const double c1 = 0.92387953251128675613, s1 = 0.38268343236508977173, h = 0.70710678118654752440;
+    cplx a[4][4];   // a[n1][k2]: DFT4 over n2 of v[n1 + 4*n2]
+#pragma unroll
+    for (int n1 = 0; n1 < 4; ++n1) {
+      cplx t[4] = {v[n1], v[n1 + 4], v[n1 + 8], v[n1 + 12]};
+      Bfly<4>::run(t);
+#pragma unroll
+      for (int k2 = 0; k2 < 4; ++k2) a[n1][k2] = t[k2];
+    }
+    // twiddle a[n1][k2] *= w16^(n1*k2)
+    const cplx w1 = make_double2(c1, -s1), w2 = make_double2(h, -h), w3 = make_double2(s1, -c1);
+    const cplx w6 = make_double2(-h, -h), w9 = make_double2(-c1, s1);
+    a[1][1] = cmul(a[1][1], w1); a[1][2] = cmul(a[1][2], w2); a[1][3] = cmul(a[1][3], w3);
+    a[2][1] = cmul(a[2][1], w2); a[2][2] = mul_mi(a[2][2]);   a[2][3] = cmul(a[2][3], w6);
+    a[3][1] = cmul(a[3][1], w3); a[3][2] = cmul(a[3][2], w6); a[3][3] = cmul(a[3][3], w9);
+#pragma unroll
+    for (int k2 = 0; k2 < 4; ++k2) {
+      cplx s[4] = {a[0][k2], a[1][k2], a[2][k2], a[3][k2]};
+      Bfly<4>::run(s);
+#pragma unroll
+      for (int k1 = 0; k1 < 4; ++k1) v[k2 + 4 * k1] = s[k1];
+    }
+  }
+};
+
+template <> struct BigBfly<18> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 9>(v); } };
+template <> struct BigBfly<20> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<4, 5>(v); } };
 
 // One radix-R stage over `nlines` independent lines living in one work buffer.
 //   element k of line l is at  W[l*ls + k*es]

@@ -218,6 +218,36 @@ def test_strip_mode_split_form_small_batches_and_large_images(b2c, oracle, torch
         p.destroy()
 
 
+def test_tuned_1d_period_family_vs_oracle(b2c, oracle, torch_cuda):
+    """1-D signals with a shared kernel on every menu period of conv_tuned1d.cu (three- and four-pass
+    schedules), rows and columns, all crop modes, odd batches (the last CTA transforms one signal), against
+    the oracle and against the any-size kernel."""
+    torch = torch_cuda
+    rng = np.random.default_rng(53)
+    cases = [(2, 480, 64, 512), (0, 600, 41, 640), (3, 768, 100, 768), (2, 1000, 40, 1024), (0, 1000, 255, 1280), (5, 1200, 300, 1536),
+             (2, 2000, 64, 2048), (0, 2100, 200, 2304), (2, 2500, 120, 2560), (7, 3000, 73, 3072), (4, 4096, 255, 4096),
+             (2, 4096, 255, 4608), (0, 4096, 1000, 5120), (2, 4096, 4096, 6144), (0, 4095, 4095, 8192), (6, 4000, 97, 4096)]
+    for k, (mode, ns, nk, P) in enumerate(cases):
+        column = k % 3 == 2
+        shape_s, shape_k = ((ns, 1), (nk, 1)) if column else ((1, ns), (1, nk))
+        p = b2c.Plan(mode, *shape_s, *shape_k)
+        assert (p.h_fft if column else p.w_fft) == P, (mode, ns, nk, p.h_fft, p.w_fft, P)
+        n = 5
+        src, ker = rng.random((n,) + shape_s), rng.random(shape_k)
+        d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+        got = {}
+        for path in (b2c.PATH_FFT, b2c.PATH_FFT_GENERIC):
+            p.set_path(path)
+            d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+            torch.cuda.synchronize()
+            got[path] = d_dst.cpu().numpy()
+        for i in (0, n - 1):
+            _check(got[b2c.PATH_FFT][i], oracle.convolve_direct8(mode, src[i], ker), ("tuned 1-D", mode, ns, nk, P, i))
+        _check(got[b2c.PATH_FFT], got[b2c.PATH_FFT_GENERIC], ("tuned 1-D vs any-size", mode, ns, nk, P))
+        p.destroy()
+
+
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
     """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
     rng = np.random.default_rng(14)
