@@ -43,7 +43,9 @@ struct Geo {
   static constexpr int LD = ((P + 2) | 1) + ((((P + 2) | 1) % 8 == 1) ? 2 : 0);   // odd, not == 1 (mod 8)
   static constexpr int KLD = (NK + 7) / 8 * 8;
   static constexpr int BPAD = KLD;
-  static constexpr int THREADS = 256;
+  // CTA size follows the work per pass: small periods run many small CTAs per SM (measured: 64 threads up to
+  // P = 48, 128 up to 80; e.g. P = 40: 74 -> 113 M conv/s, P = 80: 23.3 -> 28.5 M conv/s against 256 threads)
+  static constexpr int THREADS = P <= 48 ? 64 : P <= 80 ? 128 : 256;
   static constexpr int A_LINES = THREADS / R2;
   static constexpr int A_ROUNDS = (NK + A_LINES - 1) / A_LINES;
   static constexpr int N0 = R2 / 2 + 1;          // half-spectrum columns in the p == 0 family
@@ -61,10 +63,10 @@ struct Geo {
 };
 
 template <int R1, int R2>
-__global__ void __launch_bounds__(256, (Geo<R1, R2>::smem_bytes <= 110 * 1024 ? 2 : 1))
+__global__ void __launch_bounds__((Geo<R1, R2>::THREADS), (Geo<R1, R2>::THREADS == 64 ? 8 : Geo<R1, R2>::THREADS == 128 ? 4 : Geo<R1, R2>::smem_bytes <= 110 * 1024 ? 2 : 1))
 conv_kernel(const __grid_constant__ Params p) {
   typedef Geo<R1, R2> G;
-  constexpr int P = G::P, HALF = G::HALF, H1 = G::H1, NK = G::NK, LD = G::LD, KLD = G::KLD, BPAD = G::BPAD;
+  constexpr int HALF = G::HALF, H1 = G::H1, NK = G::NK, LD = G::LD, KLD = G::KLD, BPAD = G::BPAD;
   constexpr int THREADS = G::THREADS, A_LINES = G::A_LINES, A_ROUNDS = G::A_ROUNDS;
   cplx* Z = reinterpret_cast<cplx*>(b2c_smem_t2);
   const int t = threadIdx.x;
@@ -307,7 +309,9 @@ cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, c
 }  // namespace t2
 
 // ---- the menu: square periods with a tuned kernel (108 = 12 x 9 is conv_tuned108.cu) -------------
-#define B2C_T2_MENU(X) X(8, 5) X(8, 6) X(8, 7) X(8, 8) X(8, 9) X(10, 8) X(10, 9) X(12, 8) X(10, 10) X(14, 8) X(12, 10) X(16, 8)
+#define B2C_T2_MENU(X)                                                                                         \
+  X(8, 2) X(10, 2) X(8, 3) X(4, 7) X(8, 4) X(6, 6) X(8, 5) X(6, 7) X(8, 6) X(10, 5) X(6, 9) X(8, 7) X(10, 6) X(8, 8) \
+  X(10, 7) X(8, 9) X(10, 8) X(12, 7) X(10, 9) X(12, 8) X(10, 10) X(14, 8) X(12, 10) X(14, 9) X(16, 8)
 
 bool tuned2_has(int P) {
   switch (P) {

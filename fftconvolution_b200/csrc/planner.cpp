@@ -179,7 +179,7 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
   // square periods that have a hand-tuned kernel (conv_tuned108.cu, conv_tuned2.cu): one period for
   // both axes, about a third of the generic kernel's time at equal size (measured)
   if (!out.h.exact && !out.w.exact && out.h.fold == 0 && out.w.fold == 0 && hs > 1 && ws > 1) {
-    static const int menu[] = {40, 48, 56, 64, 72, 80, 90, 96, 100, 108, 112, 120, 128};
+    static const int menu[] = {16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128};
     const int need = std::max(out.h.min_period, out.w.min_period);
     for (int pm : menu) {
       if (pm < need) continue;
