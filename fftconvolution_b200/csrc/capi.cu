@@ -171,9 +171,17 @@ struct b2c_plan {
   cplx* work = nullptr;
   size_t work_slabs = 0;
   size_t work_slab_bytes = 0;
-  // single-image host path staging
+  // single-image host path staging: device [src | kernel | dst], pinned host [src | kernel]; the
+  // kernel half of both doubles as a cache keyed on the kernel's contents: a caller
+  // looping convolve() over one kernel (convolution_benchmark.cc:178-186) uploads and transforms it once
   double* d_one = nullptr;
   size_t d_one_bytes = 0;
+  unsigned char* h_one = nullptr;
+  size_t h_one_bytes = 0;
+  bool ker_cached = false;      // h_one / d_one hold the kernel of the previous single call
+  bool kspec_cached = false;    // ... and p->kspec holds its spectrum for the plan's current path
+  bool kspec_reuse = false;     // transient: set around the inner call when the spectrum may be reused
+  bool single_call = false;     // transient: the inner call is one image from convolve(): pick the path by latency
   // batched host pipeline
   double* d_src[kPipe] = {nullptr, nullptr, nullptr};
   double* d_ker[kPipe] = {nullptr, nullptr, nullptr};
@@ -263,8 +271,10 @@ bool tuned108_applies(const b2c_plan* p, int shared) {
 int run_tuned108(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
   const Plan2D& pl = p->pl;
   if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, work_bytes(pl)));
-  CUDA_TRY(launch_tuned108_kspec(d_ker, pl.h.n_ker, pl.w.n_ker, p->tw.tw, p->kspec, st));
-  ++g_launches;
+  if (!p->kspec_reuse) {
+    CUDA_TRY(launch_tuned108_kspec(d_ker, pl.h.n_ker, pl.w.n_ker, p->tw.tw, p->kspec, st));
+    ++g_launches;
+  }
   const int occ = tuned108_occupancy();
   if (occ < 1) return fail(B2C_ECUDA, "tuned 108x108 kernel cannot be resident");
   int grid = (int)std::min<long>(n, (long)p->ctx->sms * occ);
@@ -385,7 +395,7 @@ int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_
   }
   int launches = 0;
   CUDA_TRY(launch_tuned2(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
-                         pl.w.off, d_src, d_ker, d_dst, n, p->kspec, p->tw.tw, p->ctx->sms, st, &launches));
+                         pl.w.off, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n, p->kspec, p->tw.tw, p->ctx->sms, st, &launches));
   g_launches += launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
   return 0;
@@ -408,7 +418,7 @@ int run_tuned1d(b2c_plan* p, const double* d_src, const double* d_ker, double* d
     CUDA_TRY(cudaEventRecord(e0, st));
   }
   int launches = 0;
-  CUDA_TRY(launch_tuned1d(pl.w.P, pl.w.n_src, pl.w.n_ker, pl.w.n_dst, pl.w.off, d_src, d_ker, d_dst, n, p->kspec,
+  CUDA_TRY(launch_tuned1d(pl.w.P, pl.w.n_src, pl.w.n_ker, pl.w.n_dst, pl.w.off, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n, p->kspec,
                           p->tw.tw, p->ctx->sms, st, &launches));
   g_launches += launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
@@ -459,8 +469,10 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
   if (shared) {
     if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, wb));
     q.kspec = p->kspec;
-    CUDA_TRY(launch_kspec(q, 512, wb, st));
-    ++g_launches;
+    if (!p->kspec_reuse) {
+      CUDA_TRY(launch_kspec(q, 512, wb, st));
+      ++g_launches;
+    }
   }
   if (g_timer.on && g_timer.ev.size() < 8192) {
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
@@ -491,6 +503,8 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   while (tile > 1 && direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw) > budget2) tile = (tile + 1) / 2;
   if (direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw) > budget1)
     return fail(B2C_ESIZE, "direct kernel: %dx%d kernel does not fit in shared memory", q.hk, q.wk);
+  // a batch too small to fill the SMs with whole-image tiles: shorter tiles (8 rows = one task row per thread)
+  while (tile > 8 && n * ((q.hd + tile - 1) / tile) < (long)p->ctx->sms) tile = std::max(8, ((tile + 1) / 2 + 7) / 8 * 8);
   q.tile_h = tile;
   q.tiles_per_image = (q.hd + tile - 1) / tile;
   // Small images with a shared kernel: a CTA takes `group` whole images at a time, enough for about three
@@ -523,6 +537,19 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
 
 int effective_path(const b2c_plan* p, int shared) {
   if (p->forced_path != B2C_PATH_AUTO) return p->forced_path;
+  // One image at a time (convolve() through the header) is a latency problem, not a throughput one: the
+  // fused FFT kernels put one CTA on an image and transform the kernel first, the direct kernel spreads row
+  // tiles of the image over many SMs.  Measured per call with a pinned result buffer (tools/probe_latency.py,
+  // floor of two copies + one launch + sync = 20 us): 50x50 (*) 10x10 FFT 32-36 us, direct 24-27 us;
+  // 100x100 (*) 15x15 FFT 46 us (76 us when the kernel changes every call), direct 41 us.
+  if (p->single_call) {
+    const Plan2D& pl = p->pl;
+    const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
+    int spw;
+    if (pl.h.n_ker <= 16 && fma <= 4e6 &&
+        direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, std::min(8, pl.h.n_dst), &spw) <= 100 * 1024)
+      return B2C_PATH_DIRECT;
+  }
   return auto_path(p->pl, shared != 0);
 }
 
@@ -637,6 +664,7 @@ int b2c_plan_set_path(b2c_plan* p, int path) {
   if (path == B2C_PATH_FFT_GENERIC && p->strip_only)
     return fail(B2C_ESIZE, "b2c_plan_set_path: a transform this large only runs in strip mode");
   p->forced_path = path;
+  p->kspec_cached = false;   // another path keeps its spectrum in another layout
   return 0;
 }
 
@@ -645,6 +673,7 @@ int b2c_plan_destroy(b2c_plan* p) {
   if (p->kspec) cudaFree(p->kspec);
   if (p->work) cudaFree(p->work);
   if (p->d_one) cudaFree(p->d_one);
+  if (p->h_one) cudaFreeHost(p->h_one);
   free_pipe(p);
   if (p->pipe_ready) {
     for (int i = 0; i < kPipe; ++i) {
@@ -659,6 +688,7 @@ int b2c_plan_destroy(b2c_plan* p) {
 int b2c_convolve_batch_device(b2c_plan* p, const double* d_src, const double* d_kernel,
                               int kernel_is_shared, double* d_dst, long n_images, void* cuda_stream) {
   if (!p) return fail(B2C_EINVAL, "b2c_convolve_batch_device: null plan");
+  if (!p->kspec_reuse) p->kspec_cached = false;   // the spectrum buffer is about to hold this call's kernel
   if (n_images < 0) return fail(B2C_EINVAL, "b2c_convolve_batch_device: negative batch");
   if (p->pl.empty || n_images == 0) return 0;  // convolution_fftw.h:218-219
   if (!d_src || !d_kernel || !d_dst) return fail(B2C_EINVAL, "b2c_convolve_batch_device: null buffer");
@@ -680,17 +710,33 @@ int b2c_convolve_host(b2c_plan* p, const double* src, const double* kernel, doub
   const size_t need = up(sb) + up(kb) + up(db);
   if (p->d_one_bytes < need) {
     if (p->d_one) cudaFree(p->d_one);
-    p->d_one = nullptr; p->d_one_bytes = 0;
+    p->d_one = nullptr; p->d_one_bytes = 0; p->ker_cached = false;
     CUDA_TRY(cudaMalloc(&p->d_one, need));
     p->d_one_bytes = need;
+  }
+  if (p->h_one_bytes < up(sb) + up(kb)) {
+    if (p->h_one) cudaFreeHost(p->h_one);
+    p->h_one = nullptr; p->h_one_bytes = 0; p->ker_cached = false;
+    CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&p->h_one), up(sb) + up(kb), cudaHostAllocDefault));
+    p->h_one_bytes = up(sb) + up(kb);
   }
   char* base = reinterpret_cast<char*>(p->d_one);
   double* ds = reinterpret_cast<double*>(base);
   double* dk = reinterpret_cast<double*>(base + up(sb));
   double* dd = reinterpret_cast<double*>(base + up(sb) + up(kb));
-  CUDA_TRY(cudaMemcpyAsync(ds, src, sb, cudaMemcpyHostToDevice, 0));
-  CUDA_TRY(cudaMemcpyAsync(dk, kernel, kb, cudaMemcpyHostToDevice, 0));
-  if (int rc = b2c_convolve_batch_device(p, ds, dk, 1, dd, 1, nullptr)) return rc;
+  // one transfer from pinned staging: [src | kernel], or src alone when the kernel is the cached one
+  const bool same_kernel = p->ker_cached && memcmp(p->h_one + up(sb), kernel, kb) == 0;
+  memcpy(p->h_one, src, sb);
+  if (!same_kernel) memcpy(p->h_one + up(sb), kernel, kb);
+  CUDA_TRY(cudaMemcpyAsync(ds, p->h_one, same_kernel ? sb : up(sb) + kb, cudaMemcpyHostToDevice, 0));
+  p->kspec_reuse = same_kernel && p->kspec_cached;
+  p->single_call = true;
+  const int rc = b2c_convolve_batch_device(p, ds, dk, 1, dd, 1, nullptr);
+  p->kspec_reuse = false;
+  p->single_call = false;
+  if (rc) { p->ker_cached = false; p->kspec_cached = false; return rc; }
+  p->ker_cached = true;
+  p->kspec_cached = true;
   CUDA_TRY(cudaMemcpyAsync(dst, dd, db, cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return 0;

@@ -187,10 +187,12 @@ cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int s
   cudaFuncSetAttribute(ck, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
   Params pk = p;
   pk.src = d_ker; pk.ns = nk; pk.n_signals = 1;
-  kk<<<1, G::THREADS, G::smem_bytes, st>>>(pk, kspec);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  ++*launches;
+  if (d_ker) {   // nullptr: the spectrum of the previous call is still valid (single-call kernel cache)
+    kk<<<1, G::THREADS, G::smem_bytes, st>>>(pk, kspec);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    ++*launches;
+  }
   int occ = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ck, G::THREADS, G::smem_bytes);
   if (occ < 1) return cudaErrorLaunchOutOfResources;

@@ -291,10 +291,12 @@ cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, c
   typedef Geo<R1, R2> G;
   const size_t ksmem = sizeof(cplx) * (size_t)(wk < G::P ? wk : G::P) * G::NK;
   cudaFuncSetAttribute(kspec_kernel<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmem);
-  kspec_kernel<R1, R2><<<1, 512, ksmem, st>>>(d_ker, hk, wk, p.tw, const_cast<cplx*>(p.kspec));
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  ++*launches;
+  if (d_ker) {   // nullptr: the spectrum of the previous call is still valid (single-call kernel cache)
+    kspec_kernel<R1, R2><<<1, 512, ksmem, st>>>(d_ker, hk, wk, p.tw, const_cast<cplx*>(p.kspec));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    ++*launches;
+  }
   int occ = 0;
   cudaFuncSetAttribute(conv_kernel<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_kernel<R1, R2>, G::THREADS, G::smem_bytes);

@@ -248,6 +248,38 @@ def test_tuned_1d_period_family_vs_oracle(b2c, oracle, torch_cuda):
         p.destroy()
 
 
+def test_single_call_kernel_cache(b2c, oracle, torch_cuda):
+    """convolve() through the header re-uses the uploaded kernel and its spectrum while the caller passes the
+    same kernel contents (the reference benchmark's loop), and must notice every change: new contents in the
+    same buffer, a batch call with another kernel in between, a forced path change."""
+    torch = torch_cuda
+    rng = np.random.default_rng(61)
+    for (mode, hs, ws, hk, wk) in [(2, 50, 50, 10, 10), (2, 100, 100, 15, 15), (0, 1, 4096, 1, 255), (2, 30, 30, 3, 3), (7, 100, 100, 100, 100),
+                                   (4, 33, 35, 7, 9)]:
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        a, b = rng.random((hs, ws)), rng.random((hs, ws))
+        k1, k2 = rng.random((hk, wk)), rng.random((hk, wk))
+        want = lambda s, k: oracle.convolve_direct8(mode, s, k)
+        _check(p.convolve_host(a, k1), want(a, k1), ("first call", mode))
+        _check(p.convolve_host(b, k1), want(b, k1), ("cached kernel, new source", mode))
+        kbuf = k1.copy()
+        _check(p.convolve_host(a, kbuf), want(a, k1), ("equal contents in another buffer", mode))
+        kbuf[...] = k2
+        _check(p.convolve_host(a, kbuf), want(a, k2), ("same buffer, new contents", mode))
+        # a batch call with a third kernel overwrites the plan's spectrum
+        k3 = rng.random((hk, wk))
+        d_src, d_ker = torch.from_numpy(np.stack([a, b])).cuda(), torch.from_numpy(k3).cuda()
+        d_dst = torch.empty((2, p.h_dst, p.w_dst), dtype=torch.float64, device="cuda")
+        p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), 2, 0)
+        torch.cuda.synchronize()
+        _check(d_dst[1].cpu().numpy(), want(b, k3), ("batch call", mode))
+        _check(p.convolve_host(b, kbuf), want(b, k2), ("single call after a batch call with another kernel", mode))
+        for path in (b2c.PATH_FFT_GENERIC, b2c.PATH_FFT):
+            p.set_path(path)
+            _check(p.convolve_host(a, kbuf), want(a, k2), ("after set_path", mode, path))
+        p.destroy()
+
+
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
     """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
     rng = np.random.default_rng(14)
