@@ -35,6 +35,7 @@ cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_
 // conv_big2ds.cu
 bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, int ns_w);
 cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st);
+int big2ds_ctas_per_sm();
 bool tuned1d_has(int P);
 cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, const double* d_src, const double* d_ker,
                            double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
@@ -339,9 +340,13 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
   fill_axis(q.aw, pl.w, p->tw);
   q.scale = 1.0 / ((double)Ph * (double)Pw);
   q.src = d_src; q.ker = d_ker; q.ker_stride = shared ? 0 : (long)q.hk * q.wk; q.dst = d_dst; q.n_images = n;
-  if (tuned) { q.cols_strip = 32; q.ldc = 64; }   // conv_big2ds.cu: fixed strips, S and K columns in two dense arrays
+  const int ctas = tuned ? big2ds_ctas_per_sm() : 1;
+  if (tuned) {   // conv_big2ds.cu: fixed strips, S and K columns in two dense arrays
+    q.cols_strip = ctas == 2 ? 16 : 32; q.ldc = 2 * q.cols_strip;
+    q.rows_chunk = ctas == 2 ? 32 : 64;
+  }
   const size_t smem = sizeof(cplx) * std::max((size_t)q.rows_chunk * q.ldw, (size_t)Ph * q.ldc);
-  const int grid = (int)std::max<long>(1, std::min<long>(n, split ? group : (long)p->ctx->sms));
+  const int grid = (int)std::max<long>(1, std::min<long>(n, split ? group : (long)p->ctx->sms * ctas));
   const size_t slab_per_cta = sizeof(cplx) * (size_t)std::max(q.hs + hke, q.rows_y) * q.half_w;   // Y overwrites S|K strip by strip
   const size_t slabs = (size_t)grid;   // one per resident CTA (persistent form) or per image (split form)
   if (p->work_slabs < slabs || p->work_slab_bytes < slab_per_cta) {

@@ -76,12 +76,15 @@ template <int P, int R, int N, bool INV>
 __device__ __forceinline__ void stage(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane,
                                       int nsplit = 1 << 30, int kjump = 0) {
   constexpr int M = N / R, PER_LINE = P / R, TSTEP = P / N;
-  const int ntrips = (nlines + 31) >> 5;
-  for (int task = warp; task < PER_LINE * ntrips; task += nwarps) {      // warp-uniform
-    const int t = task / ntrips, line = ((task - t * ntrips) << 5) + lane;
+  // 32 lines per warp task, or -- for strips of at most 16 lines -- two butterflies of 16 lines each
+  const int lpt = nlines <= 16 ? 16 : 32, subs = 32 / lpt;
+  const int ntrips = (nlines + lpt - 1) / lpt, total = PER_LINE * ntrips;
+  for (int wt = warp; wt * subs < total; wt += nwarps) {
+    const int task = wt * subs + lane / lpt;
+    const int t = task / ntrips, line = (task - t * ntrips) * lpt + lane % lpt;
     const int b = t / M, j = t - b * M;
     cplx* base = W + (b * N + j) * es;
-    if (line < nlines) {
+    if (task < total && line < nlines) {
       cplx* p = base + line * ls + (line >= nsplit ? kjump : 0);   // lines past nsplit live in a second array
       cplx v[R];
 #pragma unroll
@@ -132,10 +135,12 @@ struct Fft {
   // through shared memory fewer than forward-pass / product / backward-pass.
   static __device__ __forceinline__ void middle(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane,
                                                 int koff, double scale) {
-    const int ntrips = (nlines + 31) >> 5;
-    for (int task = warp; task < R0 * ntrips; task += nwarps) {
-      const int b = task / ntrips, line = ((task - b * ntrips) << 5) + lane;
-      if (line < nlines) {
+    const int lpt = nlines <= 16 ? 16 : 32, subs = 32 / lpt;
+    const int ntrips = (nlines + lpt - 1) / lpt, total = R0 * ntrips;
+    for (int wt = warp; wt * subs < total; wt += nwarps) {
+      const int task = wt * subs + lane / lpt;
+      const int b = task / ntrips, line = (task - b * ntrips) * lpt + lane % lpt;
+      if (task < total && line < nlines) {
         cplx* ps = W + b * R1 * es + line * ls;
         cplx k[R1], v[R1];
 #pragma unroll
@@ -172,8 +177,8 @@ __device__ __forceinline__ double wrapped_tap(const BigParams& p, const double* 
   return acc;
 }
 
-template <int P, int R0, int R1, int NT>
-__global__ void __launch_bounds__(NT, 1) conv_kernel(const __grid_constant__ BigParams p) {
+template <int P, int R0, int R1, int NT, int CTAS, int CS>
+__global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ BigParams p) {
   typedef Fft<P, R0, R1> F;
   cplx* W = reinterpret_cast<cplx*>(b2c_smem_bigs);
   const int lane = threadIdx.x & 31;
@@ -188,7 +193,6 @@ __global__ void __launch_bounds__(NT, 1) conv_kernel(const __grid_constant__ Big
   // followed by [hke][nc] K rows -- one contiguous run per transfer; the strip's Y[rows_y][nc] later
   // replaces the block in place.
   constexpr int NQ = 1;                                      // pieces per bulk transfer (more pieces measured no faster)
-  constexpr int CS = 32;                                     // half-spectrum columns per strip
   const int rows_total = max(p.hs + hke, p.rows_y);
   cplx* slab = p.slab + (size_t)blockIdx.x * (size_t)rows_total * HW;
   __shared__ unsigned long long bar_storage;
@@ -359,12 +363,24 @@ bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, in
   return Ph == 200 && Pw == 200;
 }
 
-// 384 threads: the fused middle pass keeps 2 x 20 complex values per thread (168 registers)
+// Two shapes: one CTA of 384 threads per SM with 32-column strips and 64-row chunks, or two CTAs of 192
+// threads with 16-column strips and 32-row chunks (one copies while the other transforms).  168 registers
+// per thread either way: the fused middle pass keeps 2 x 20 complex values.
+int big2ds_ctas_per_sm() {
+  static const int v = getenv("B2C_BIG_CTAS") ? atoi(getenv("B2C_BIG_CTAS")) : 2;   // measured: 1.53 vs 1.63 M conv/s
+  return v == 1 ? 1 : 2;
+}
+
 cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st) {
-  constexpr int NT = 384;
-  auto kern = bigs::conv_kernel<200, 10, 20, NT>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  kern<<<grid, NT, smem, st>>>(p);
+  if (big2ds_ctas_per_sm() == 2) {
+    auto kern = bigs::conv_kernel<200, 10, 20, 192, 2, 16>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<grid, 192, smem, st>>>(p);
+  } else {
+    auto kern = bigs::conv_kernel<200, 10, 20, 384, 1, 32>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<grid, 384, smem, st>>>(p);
+  }
   return cudaGetLastError();
 }
 
