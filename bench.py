@@ -340,6 +340,25 @@ def run_b2c_arm(args):
                             n_sample, BATCH,
                             "unmodified over stand-in FFT (no libfftw3 on box)" if kind == "reference" else "restated (oracle port)",
                             cores, dt)}
+        try:   # one core beside all cores, and the reference's nested loops (convolution_std.h)
+            n1 = max(64, int(rate / cores * 2.0))
+            r1, _, d1 = time_cpu_reference(n1, 1)
+            cpu_baseline["one_core"] = {"value": r1, "unit": UNIT, "cores": 1, "sample": "%d images (%.1f s)" % (n1, d1)}
+            import _oracle
+            ref = _oracle.load_ref()
+            if ref is not None:
+                import numpy as np
+                ns = 64 * cores
+                s_src = _oracle.splitmix_uniform(SEED, 0, ns * H * W).reshape(ns, H, W)
+                t0 = time.perf_counter()
+                out_std = ref.batch_std(1, s_src, ker, threads=cores)   # STD_Convolution::LINEAR_SAME
+                d_std = time.perf_counter() - t0
+                out_fft = ref.batch_fftw(MODE_LINEAR_SAME, s_src[:4], ker, threads=1)
+                cpu_baseline["nested_loops"] = {"value": ns / d_std, "unit": UNIT, "cores": cores,
+                                                "sample": "%d images, convolution_std.h unmodified (%.2f s)" % (ns, d_std),
+                                                "agrees_with_fft_path": bool(np.allclose(out_std[:4], out_fft, rtol=1e-10, atol=1e-10))}
+        except Exception as ex:
+            cpu_baseline["one_core"] = {"error": str(ex)[:100]}
         try:
             n2 = 4096
             r2, d2 = time_cpu_scipy_port(n2, cores)

@@ -77,6 +77,22 @@ class _Lib:
         return dst
 
 
+    def batch_std(self, std_mode, src, ker, threads=1):
+        """The reference's nested loops (convolution_std.h) over a batch; unmodified-reference library only."""
+        assert self.prefix == "ref"
+        n, hs, ws = src.shape
+        hk, wk = ker.shape[-2:]
+        shp = {0: (hs + hk - 1, ws + wk - 1), 1: (hs, ws), 2: (hs - hk + 1, ws - wk + 1), 3: (hs, ws),
+               4: (hs + hk - 1, ws + wk - 1)}[std_mode]
+        dst = np.zeros((n,) + shp)
+        fn = self.L.ref_std_batch
+        fn.argtypes = [ctypes.c_int] * 5 + [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                            ctypes.c_long, ctypes.c_int]
+        src, ker = np.ascontiguousarray(src), np.ascontiguousarray(ker)
+        fn(std_mode, hs, ws, hk, wk, src.ctypes.data, ker.ctypes.data, 1 if ker.ndim == 2 else 0, dst.ctypes.data, n, threads)
+        return dst
+
+
 def build_oracle():
     subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
 
