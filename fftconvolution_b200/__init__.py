@@ -32,5 +32,6 @@ from .convolution import (  # noqa: F401
     clear_workspace,
     find_closest_factor,
     smooth_size,
+    multi_convolve_batch_host,
 )
 from .partition import partition, checksum_device, fill_uniform_device  # noqa: F401

@@ -23,7 +23,7 @@ SYMBOLS = [
     "b2c_convolve_host", "b2c_convolve_batch_host", "b2c_convolve_batch_device",
     "b2c_convolve_batch_device_static",
     "b2c_find_closest_factor", "b2c_smooth_size", "b2c_partition", "b2c_checksum_device",
-    "b2c_fill_uniform_device", "b2c_host_alloc", "b2c_host_free", "b2c_set_device",
+    "b2c_fill_uniform_device", "b2c_multi_convolve_batch_host", "b2c_host_alloc", "b2c_host_free", "b2c_set_device",
     "b2c_launch_count", "b2c_kernel_timer", "b2c_kernel_timer_read", "b2c_last_error", "b2c_version",
 ]
 

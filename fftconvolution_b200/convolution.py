@@ -90,6 +90,27 @@ class Plan:
             pass
 
 
+def multi_convolve_batch_host(mode, src, kernel, n_devices=0):
+    """Shard a host-resident batch over the GPUs of this process (b2c_multi_convolve_batch_host): one
+    host thread, plan and pipeline per device, contiguous shards, no inter-GPU traffic."""
+    src = np.ascontiguousarray(src, dtype=np.float64)
+    kernel = np.ascontiguousarray(kernel, dtype=np.float64)
+    n, hs, ws = src.shape
+    shared = 1 if kernel.ndim == 2 else 0
+    hk, wk = kernel.shape[-2:]
+    assert shared or kernel.shape[0] == n
+    p = Plan(mode, hs, ws, hk, wk)
+    hd, wd = p.h_dst, p.w_dst
+    p.destroy()
+    dst = np.zeros((n, hd, wd), dtype=np.float64)
+    L = lib()
+    L.b2c_multi_convolve_batch_host.argtypes = [ctypes.c_int] * 5 + [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                                    ctypes.c_void_p, ctypes.c_long, ctypes.c_int]
+    check(L.b2c_multi_convolve_batch_host(int(mode), hs, ws, hk, wk, src.ctypes.data, kernel.ctypes.data, shared,
+                                          dst.ctypes.data if dst.size else None, n, int(n_devices)))
+    return dst
+
+
 class Workspace:
     """Mirror of FFTW_Convolution::Workspace (convolution_fftw.h:29-42): the fields callers read
     are ``dst``, ``h_dst``, ``w_dst``; ``h_fftw``/``w_fftw`` hold the new planner's periods."""

@@ -12,6 +12,7 @@
 #include <map>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/b2conv.h"
@@ -599,6 +600,47 @@ int b2c_partition(long n, int world, int rank, long* begin, long* end) {
   const long per = (n + world - 1) / world;  // GPU g owns [g*ceil(N/G), min(N,(g+1)*ceil(N/G)))
   *begin = std::min(n, per * rank);
   *end = std::min(n, per * (rank + 1));
+  return 0;
+}
+
+// In-process form of the batch partitioner (SURVEY 8b "b2c_multi_*", 8e): a C++ caller of the header lives
+// in ONE process, so the contiguous shards of b2c_partition are run by one host thread per device, each with
+// its own plan and its own H2D || compute || D2H pipeline.  No inter-GPU traffic.
+int b2c_multi_convolve_batch_host(int mode, int h_src, int w_src, int h_kernel, int w_kernel, const double* src,
+                                  const double* kernel, int kernel_is_shared, double* dst, long n_images,
+                                  int n_devices) {
+  if (n_images < 0) return fail(B2C_EINVAL, "b2c_multi_convolve_batch_host: negative batch");
+  int have = 0;
+  CUDA_TRY(cudaGetDeviceCount(&have));
+  if (n_devices == 0) n_devices = have;
+  if (n_devices < 1 || n_devices > have)
+    return fail(B2C_EINVAL, "b2c_multi_convolve_batch_host: %d devices requested, %d present", n_devices, have);
+  if (n_images == 0) return 0;
+  if (!src || !kernel || !dst) return fail(B2C_EINVAL, "b2c_multi_convolve_batch_host: null buffer");
+  std::vector<int> rc(n_devices, 0);
+  std::vector<std::string> msg(n_devices);
+  auto work = [&](int g) {
+    b2c_plan* plan = nullptr;
+    long begin = 0, end = 0;
+    int r = b2c_set_device(g);
+    if (!r) r = b2c_plan_create(&plan, mode, h_src, w_src, h_kernel, w_kernel);
+    if (!r) r = b2c_partition(n_images, n_devices, g, &begin, &end);
+    if (!r && end > begin) {
+      int hf, wf, hd, wd;
+      b2c_plan_query(plan, &hf, &wf, &hd, &wd);
+      const size_t sn = (size_t)h_src * w_src, kn = (size_t)h_kernel * w_kernel, dn = (size_t)hd * wd;
+      r = b2c_convolve_batch_host(plan, src + sn * begin, kernel + (kernel_is_shared ? 0 : kn * begin), kernel_is_shared,
+                                  dst + dn * begin, end - begin);
+    }
+    if (r) msg[g] = b2c_last_error();   // the message lives in this worker thread
+    if (plan) b2c_plan_destroy(plan);
+    rc[g] = r;
+  };
+  std::vector<std::thread> pool;
+  for (int g = 0; g < n_devices; ++g) pool.emplace_back(work, g);
+  for (auto& t : pool) t.join();
+  for (int g = 0; g < n_devices; ++g)
+    if (rc[g]) return fail(rc[g], "device %d: %s", g, msg[g].c_str());
   return 0;
 }
 

@@ -109,6 +109,15 @@ int b2c_smooth_size(int n);
  * `world` (one process per GPU; no data-path collective). */
 int b2c_partition(long n, int world, int rank, long* begin, long* end);
 
+/* The same partitioner inside ONE process (no reference counterpart; the reference is single-threaded,
+ * convolution_benchmark.cc:178-186 loops over convolve): the batch in host memory is cut into the contiguous
+ * shards of b2c_partition and device g of `n_devices` (0 = all visible devices) convolves shard g on its own
+ * host thread, plan and copy/compute pipeline.  Arguments as b2c_plan_create + b2c_convolve_batch_host.
+ * Pinned host buffers (b2c_host_alloc) are needed for full PCIe rate. */
+int b2c_multi_convolve_batch_host(int mode, int h_src, int w_src, int h_kernel, int w_kernel, const double* src,
+                                  const double* kernel, int kernel_is_shared, double* dst, long n_images,
+                                  int n_devices);
+
 /* Order-independent verification checksum of n doubles on the current device: wrapping 64-bit
  * sum and xor of the IEEE-754 bit patterns, plus the plain double sum.  out = 3 x 64 bit on the
  * HOST: {sum_bits, xor_bits, double_sum_bits}.  Synchronous on `cuda_stream`.  Ranks combine

@@ -280,6 +280,32 @@ def test_single_call_kernel_cache(b2c, oracle, torch_cuda):
         p.destroy()
 
 
+def test_multi_device_batch_in_one_process(b2c, oracle, torch_cuda):
+    """b2c_multi_convolve_batch_host: contiguous shards of a host batch, one host thread + plan + pipeline per
+    device of THIS process.  Runs with however many GPUs are visible (1 on the test box: the shard logic is
+    also covered on CPU by tests/test_partition_gloo.py); must equal the single-plan batch (bit for bit on one device)."""
+    torch = torch_cuda
+    rng = np.random.default_rng(71)
+    ndev = torch.cuda.device_count()
+    for (mode, hs, ws, hk, wk, n, shared) in [(2, 40, 36, 7, 9, 37, 1), (7, 20, 20, 20, 20, 11, 0), (0, 1, 700, 1, 90, 9, 1)]:
+        src = rng.random((n, hs, ws))
+        ker = rng.random((hk, wk)) if shared else rng.random((n, hk, wk))
+        p = b2c.Plan(mode, hs, ws, hk, wk)
+        want = p.convolve_batch_host(src, ker)
+        p.destroy()
+        for nd in sorted({0, 1, ndev}):
+            got = b2c.multi_convolve_batch_host(mode, src, ker, n_devices=nd)
+            if (ndev if nd == 0 else nd) == 1:
+                assert np.array_equal(got, want), (mode, nd)
+            else:   # a shard that starts on an odd image pairs images differently in the two-per-transform kernels
+                _check(got, want, ("multi-device vs one plan", mode, nd))
+        _check(want[n - 1], oracle.convolve_direct8(mode, src[n - 1], ker if shared else ker[n - 1]), ("multi", mode))
+    with pytest.raises(b2c.B2CError) as e:
+        b2c.multi_convolve_batch_host(2, np.zeros((2, 8, 8)), np.zeros((3, 3)), n_devices=ndev + 1)
+    assert e.value.code == 1 and "devices requested" in str(e.value)
+    torch.cuda.set_device(0)
+
+
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
     """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
     rng = np.random.default_rng(14)
