@@ -204,18 +204,18 @@ size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (si
 
 // Crossover between the direct kernel and the FFT chain: two time models per image, fitted to the
 // measured sweep profiles/r01_crossover.csv (tools/crossover_sweep.py).
-//   direct: max(HBM stream at 3.0 TB/s, FMAs at 5.8 TFMA/s) for the 8-rows-per-thread variant,
+//   direct: max(HBM stream at 3.0 TB/s (2.3 below 64 rows), FMAs at 4.8 TFMA/s) for the 8-rows-per-thread variant,
 //           HBM at 2.5 TB/s + FMAs at 3.1 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image
 //           (0.4 ns with a shared kernel: small images are processed in groups per CTA);
 //           kernels taller than 16 rows run a general variant that is about 4x slower.
 //   FFT   : planner cost units x 0.15 ps, never below 10 ns per image (generic kernel); 5.6-6.5 ps per point
-//           of the period + 1.5 ns for the tuned square-period kernels; 9.5 ps per point for the tuned 1-D kernels.
+//           of the period + 1 ns for the tuned square-period kernels; 9.5 ps per point for the tuned 1-D kernels.
 int auto_path(const Plan2D& pl, bool shared) {
   const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
   const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
   double t_direct;
   const double per_image = shared ? 0.4e-9 : 4e-9;
-  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / 3.0e12, fma / 5.8e12) + per_image;
+  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / (pl.h.n_dst >= 64 ? 3.0e12 : 2.3e12), fma / 4.8e12) + per_image;
   else t_direct = bytes / 2.5e12 + fma / 3.1e12 + per_image;
   if (pl.h.n_ker > 16) t_direct *= 4.0;
   const double rows = (double)pl.h.n_src + pl.h.lin;
@@ -223,12 +223,12 @@ int auto_path(const Plan2D& pl, bool shared) {
   if (shared) cost *= 0.5;  // two images per transform
   const bool tuned = shared && pl.h.P == pl.w.P && (pl.h.P == 108 || tuned2_has(pl.h.P)) && pl.h.fold == 0 &&
                      pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
-  // tuned kernels: 5.6 ps (P <= 80) or 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 1.5 ns
+  // tuned kernels: 5.6 ps (P <= 80) or 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 1 ns
   const double pp = (double)pl.h.P * pl.w.P;
   // tuned 1-D kernels (conv_tuned1d.cu): 9.5 ps per point of the period
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
                       pl.w.fold == 0 && pl.w.kwrap == pl.w.P && pl.w.n_ker <= pl.w.P;
-  const double t_fft = tuned    ? (pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.5e-9
+  const double t_fft = tuned    ? (pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.0e-9
                        : tuned1 ? 9.5e-12 * pl.w.P + 0.5e-9
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory

@@ -82,8 +82,7 @@ __device__ __forceinline__ void big_phase_r(const BigParams& p, const BigCtx& x,
     }
   }
   __syncthreads();
-  if (is_static_200(p.aw)) StaticFft<200, 5, 5, 8, 1>::forward(p.aw.tw, W, 1, p.ldw, nr, false);
-  else fft_forward(p.aw, W, 1, p.ldw, nr, false);
+  fft_forward(p.aw, W, 1, p.ldw, nr, false);
   // Z = S + iK  =>  S(v) = (Z(v) + conj Z(-v)) / 2,  K(v) = -i (Z(v) - conj Z(-v)) / 2
   const int HW = x.HW;
   for (int idx = threadIdx.x; idx < nr * HW; idx += blockDim.x) {
@@ -123,8 +122,7 @@ __device__ __forceinline__ void big_phase_c(const BigParams& p, const BigCtx& x,
     }
   }
   __syncthreads();
-  if (is_static_200(p.ah)) StaticFft<200, 5, 5, 8, 1>::forward(p.ah.tw, W, p.ldc, 1, 2 * nc, true);
-  else fft_forward(p.ah, W, p.ldc, 1, 2 * nc, true);
+  fft_forward(p.ah, W, p.ldc, 1, 2 * nc, true);
   for (int idx = threadIdx.x; idx < Ph * nc; idx += blockDim.x) {   // convolution_fftw.h:195-204, 210-211
     const int r = idx / nc, c = idx - r * nc;
     const cplx s = W[r * p.ldc + c], kk = W[r * p.ldc + nc + c];
@@ -132,8 +130,7 @@ __device__ __forceinline__ void big_phase_c(const BigParams& p, const BigCtx& x,
     W[r * p.ldc + c] = make_double2(y.x * p.scale, y.y * p.scale);
   }
   __syncthreads();
-  if (is_static_200(p.ah)) StaticFft<200, 5, 5, 8, 1>::backward(p.ah.tw, W, p.ldc, 1, nc, true);
-  else fft_backward(p.ah, W, p.ldc, 1, nc, true);
+  fft_backward(p.ah, W, p.ldc, 1, nc, true);
   for (int idx = threadIdx.x; idx < p.rows_y * nc; idx += blockDim.x) {
     const int r = idx / nc, c = idx - r * nc;
     x.slabY[(size_t)r * HW + v0 + c] = W[r * p.ldc + c];
@@ -171,8 +168,7 @@ __device__ __forceinline__ void big_phase_rp(const BigParams& p, const BigCtx& x
       if (dstpos[u] >= 0) W[dstpos[u]] = make_double2(y0[u].x - y1[u].y, y0[u].y + y1[u].x);   // Y0 + i*Y1
   }
   __syncthreads();
-  if (is_static_200(p.aw)) StaticFft<200, 5, 5, 8, 1>::backward(p.aw.tw, W, 1, p.ldw, nq, false);
-  else fft_backward(p.aw, W, 1, p.ldw, nq, false);
+  fft_backward(p.aw, W, 1, p.ldw, nq, false);
   for (int idx = threadIdx.x; idx < 2 * nq * p.wd; idx += blockDim.x) {
     const int ri = fast_div(idx, p.wd, x.inv_wd), j = idx - ri * p.wd;
     const int i = 2 * q0 + ri;

@@ -281,11 +281,11 @@ __device__ __forceinline__ void fft_stage(cplx* W, int es, int ls, int nlines, i
       }
 #pragma unroll
       for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
-      Bfly<R>::run(v);
+      BigBfly<R>::run(v);
 #pragma unroll
       for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
     } else {
-      Bfly<R>::run(v);
+      BigBfly<R>::run(v);
       if (j != 0) {
 #pragma unroll
         for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(&tw[j * q * tstep]));
@@ -304,8 +304,12 @@ __device__ __forceinline__ void fft_stage_dispatch(int R, cplx* W, int es, int l
     case 3: fft_stage<3, INV>(W, es, ls, nlines, P, n, tw, lf); break;
     case 4: fft_stage<4, INV>(W, es, ls, nlines, P, n, tw, lf); break;
     case 5: fft_stage<5, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 6: fft_stage<6, INV>(W, es, ls, nlines, P, n, tw, lf); break;
     case 7: fft_stage<7, INV>(W, es, ls, nlines, P, n, tw, lf); break;
     case 8: fft_stage<8, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 9: fft_stage<9, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 10: fft_stage<10, INV>(W, es, ls, nlines, P, n, tw, lf); break;
+    case 12: fft_stage<12, INV>(W, es, ls, nlines, P, n, tw, lf); break;
   }
 }
 
@@ -346,38 +350,5 @@ __device__ __forceinline__ void fft_backward(const AxisDev& ax, cplx* W, int es,
   }
 }
 
-// Compile-time schedules: the same stages with every length, stride factor and radix a literal, so
-// the compiler folds the index arithmetic (divisions by constants, twiddle steps) that the run-time
-// schedule pays per butterfly.  Used where a plan's period is in the small menu below.
-template <int P, int R0, int R1, int R2, int R3>
-struct StaticFft {
-  static_assert(P == R0 * R1 * R2 * R3, "schedule must multiply out to the period");
-  static __device__ __forceinline__ void forward(const cplx* __restrict__ tw, cplx* W, int es, int ls, int nlines, bool lf) {
-    int n = P;
-    one<R0, false>(tw, W, es, ls, nlines, n, lf); n /= R0;
-    if (R1 > 1) { one<R1, false>(tw, W, es, ls, nlines, n, lf); n /= R1; }
-    if (R2 > 1) { one<R2, false>(tw, W, es, ls, nlines, n, lf); n /= R2; }
-    if (R3 > 1) { one<R3, false>(tw, W, es, ls, nlines, n, lf); }
-  }
-  static __device__ __forceinline__ void backward(const cplx* __restrict__ tw, cplx* W, int es, int ls, int nlines, bool lf) {
-    if (R3 > 1) one<R3, true>(tw, W, es, ls, nlines, R3, lf);
-    if (R2 > 1) one<R2, true>(tw, W, es, ls, nlines, R3 * R2, lf);
-    if (R1 > 1) one<R1, true>(tw, W, es, ls, nlines, R3 * R2 * R1, lf);
-    one<R0, true>(tw, W, es, ls, nlines, P, lf);
-  }
-  template <int R, bool INV>
-  static __device__ __forceinline__ void one(const cplx* __restrict__ tw, cplx* W, int es, int ls, int nlines, int n, bool lf) {
-    if (R > 1) {
-      const bool stage_lf = lf || nlines >= 16 || (n / R < 8 && nlines >= 8);
-      fft_stage<(R > 1 ? R : 2), INV>(W, es, ls, nlines, P, n, tw, stage_lf);
-      __syncthreads();
-    }
-  }
-};
-
-// true when (P, radix schedule) is {200: 5,5,8}; the planner's radix_schedule() produces exactly this
-__device__ __forceinline__ bool is_static_200(const AxisDev& ax) {
-  return ax.P == 200 && ax.nstages == 3 && ax.radix[0] == 5 && ax.radix[1] == 5 && ax.radix[2] == 8;
-}
 
 }  // namespace b2c

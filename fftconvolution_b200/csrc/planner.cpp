@@ -19,19 +19,9 @@ int next_smooth2357(int n) {
   return n;
 }
 
-int radix_schedule(int n, int* radix) {
-  int e2 = 0, ns = 0;
-  int rem = n;
-  while (rem % 2 == 0) { rem /= 2; ++e2; }
-  // ascending radices: the last (largest) stage is the one that needs no twiddles
-  if (e2 % 3 == 1) { radix[ns++] = 2; e2 -= 1; }
-  while (rem % 3 == 0) { radix[ns++] = 3; rem /= 3; }
-  if (e2 % 3 == 2) { radix[ns++] = 4; e2 -= 2; }
-  while (rem % 5 == 0) { radix[ns++] = 5; rem /= 5; }
-  while (rem % 7 == 0) { radix[ns++] = 7; rem /= 7; }
-  while (e2 >= 3) { radix[ns++] = 8; e2 -= 3; }
-  return ns;
-}
+// Radices the any-size kernels have a register butterfly for (fft_device.cuh: BigBfly).
+// Radix 14 and 16 butterflies exist but spill in the 128-register any-size kernels (measured slower).
+static const int kRadices[] = {12, 10, 9, 8, 7, 6, 5, 4, 3, 2};
 
 static double butterfly_cost(int r) {
   switch (r) {
@@ -39,10 +29,46 @@ static double butterfly_cost(int r) {
     case 3: return 12;
     case 4: return 16;
     case 5: return 36;
+    case 6: return 36;     // 2 x 3 prime-factor
     case 7: return 66;
     case 8: return 56;
+    case 9: return 100;    // 3 x 3 with four internal twiddles
+    case 10: return 92;    // 2 x 5 prime-factor
+    case 12: return 100;   // 3 x 4 prime-factor
   }
   return 1e9;
+}
+
+// Cheapest schedule: fewest passes first (every pass is a trip through shared memory and a barrier),
+// then the cheapest butterflies per point.
+static void search_schedule(int n, int max_radix, int depth, int* cur, int* best, int* best_len, double cost,
+                            double* best_cost) {
+  if (n == 1) {
+    const double total = cost + 1e6 * depth;
+    if (total < *best_cost) {
+      *best_cost = total;
+      *best_len = depth;
+      for (int i = 0; i < depth; ++i) best[i] = cur[i];
+    }
+    return;
+  }
+  if (depth >= kMaxStages) return;
+  for (int r : kRadices) {
+    if (r > max_radix || n % r) continue;   // non-increasing radices: each multiset is visited once
+    cur[depth] = r;
+    search_schedule(n / r, r, depth + 1, cur, best, best_len, cost + butterfly_cost(r) / r, best_cost);
+  }
+}
+
+int radix_schedule(int n, int* radix) {
+  if (n <= 1) return 0;
+  int cur[kMaxStages], best[kMaxStages], len = 0;
+  double best_cost = 1e30;
+  search_schedule(n, 12, 0, cur, best, &len, 0.0, &best_cost);
+  // ascending radices: the last (largest) stage is the one that needs no twiddles
+  std::sort(best, best + len);
+  for (int i = 0; i < len; ++i) radix[i] = best[i];
+  return len;
 }
 
 double fft_cost(int n) {

@@ -3,7 +3,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["B2C_LIB_PATH"] = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "build", "variants", "bigs_trace.so")
 import torch, fftconvolution_b200 as b2c
 torch.cuda.set_device(0)
-n = 148 * 8
+n = 296 * 8
 plan = b2c.Plan(b2c.CIRCULAR_FULL, 100, 100, 100, 100)
 src = torch.rand((n, 100, 100), dtype=torch.float64, device="cuda"); ker = torch.rand_like(src)
 dst = torch.empty((n, 199, 199), dtype=torch.float64, device="cuda")
