@@ -29,7 +29,7 @@ int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 // conv_direct.cu
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int group = 1);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
-int occupancy_direct(int hk, int hd, size_t smem);
+int occupancy_direct(int hk, int hd, bool wrap, size_t smem);
 // conv_big2d.cu
 cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_t st, int* launches);
@@ -504,7 +504,7 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   q.kernel_is_shared = shared;
   q.src = d_src; q.ker = d_ker; q.dst = d_dst; q.n_images = n;
   // largest row tile that leaves room for two CTAs per SM, else the largest that fits at all
-  const size_t budget2 = (size_t)p->ctx->smem_optin / 2 - 1024, budget1 = (size_t)p->ctx->smem_optin;
+  const size_t budget2 = (size_t)p->ctx->smem_optin / 2 - 1024, budget1 = (size_t)p->ctx->smem_optin;   // smaller tiles measured slower
   int tile = q.hd, spw = 0;
   while (tile > 1 && direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw) > budget2) tile = (tile + 1) / 2;
   if (direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw) > budget1)
@@ -525,7 +525,7 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   }
   const size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw, q.group);
   q.sp_w = spw;
-  int occ = occupancy_direct(q.hk, q.hd, smem);
+  int occ = occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);

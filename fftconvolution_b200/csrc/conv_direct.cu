@@ -26,7 +26,7 @@ __device__ __forceinline__ int wrap_index(int x, int m) {
 
 // HK > 0: compile-time kernel height; HK == 0: run-time height (general variant).
 // TI: output rows per thread (8 for images, 1 for 1-D row signals and very short images).
-template <int HK, int TI>
+template <int HK, int TI, bool WRAP>
 __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_constant__ DirectParams p) {
   double* kflip = reinterpret_cast<double*>(b2c_smem_direct);   // [wk][hk_pad]: column-major, flipped
   const int hk = HK > 0 ? HK : p.hk;
@@ -63,25 +63,28 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
     const int cols = p.wd + p.wk - 1;
     const int nelem = rows * pitch;            // staged doubles per image
     const int nall = ng * nelem;
-    const float inv_pitch = 1.0f / (float)pitch, inv_nelem = 1.0f / (float)nelem;
+    // Each thread walks the staged elements idx = tid, tid + 256, ... keeping (image g, row u, column v)
+    // by increments (no division per element); eight independent global loads are in flight per thread.
+    const int step_u = kDirectThreads / pitch, step_v = kDirectThreads - step_u * pitch;   // 256 = step_u * pitch + step_v
+    int u = threadIdx.x / pitch, v = threadIdx.x - u * pitch, g = 0;
+    if (group > 1) { g = u / rows; u -= g * rows; }
+    const int sr0 = i0 + p.off_h - (hk - 1), sc0 = p.off_w - (p.wk - 1);
     constexpr int SU = 8;
     for (int base = threadIdx.x; base < nall; base += SU * kDirectThreads) {
       double vals[SU];
 #pragma unroll
       for (int k = 0; k < SU; ++k) {
-        const int idx = base + k * kDirectThreads;
         double val = 0.0;
-        if (idx < nall) {
-          const int g = group > 1 ? fast_div(idx, nelem, inv_nelem) : 0;
-          const int rem = idx - g * nelem;
-          const int u = fast_div(rem, pitch, inv_pitch), v = rem - u * pitch;
-          int sr = i0 + u + p.off_h - (hk - 1);
-          int sc = v + p.off_w - (p.wk - 1);
-          if (p.wrap_h) sr = wrap_index(sr, p.wrap_h);
-          if (p.wrap_w) sc = wrap_index(sc, p.wrap_w);
-          if (v < cols && sr >= 0 && sr < p.hs && sc >= 0 && sc < p.ws) val = __ldg(a + (size_t)g * src_sz + (size_t)sr * p.ws + sc);
+        if (base + k * kDirectThreads < nall) {
+          int sr = sr0 + u, sc = sc0 + v;
+          if (WRAP) { sr = wrap_index(sr, p.wrap_h); sc = wrap_index(sc, p.wrap_w); }
+          if (v < cols && (unsigned)sr < (unsigned)p.hs && (unsigned)sc < (unsigned)p.ws)
+            val = __ldg(a + ((long)g * (long)src_sz + (long)(sr * p.ws + sc)));
         }
         vals[k] = val;
+        v += step_v; u += step_u;
+        if (v >= pitch) { v -= pitch; ++u; }
+        if (group > 1) { while (u >= rows) { u -= rows; ++g; } }
       }
 #pragma unroll
       for (int k = 0; k < SU; ++k) {
@@ -102,20 +105,34 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
       double acc[TI];
 #pragma unroll
       for (int t = 0; t < TI; ++t) acc[t] = 0.0;
-      const double* col = S + (size_t)g * nelem + (size_t)r0 * pitch + j;
+      const double* col = S + (g * nelem + r0 * pitch + j);       // 32-bit offsets into shared memory
       if (HK > 0) {
-        // rows beyond the tile's halo are never read for outputs that exist: clamp the window
-        const int last = rows - 1 - r0;   // highest valid window index
-        for (int kc = 0; kc < p.wk; ++kc) {
-          double w[TI + (HK > 0 ? HK : 1) - 1];
+        const int last = rows - 1 - r0;   // highest staged row of this window (rows past it feed no existing output)
+        if (last >= TI + HK - 2) {        // whole window staged: no clamping
+          for (int kc = 0; kc < p.wk; ++kc) {
+            double w[TI + (HK > 0 ? HK : 1) - 1];
 #pragma unroll
-          for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[(size_t)min(u, last) * pitch + kc];
-          const double* kv = kflip + kc * hk_pad;
+            for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[u * pitch + kc];
+            const double* kv = kflip + kc * hk_pad;
 #pragma unroll
-          for (int kr = 0; kr < HK; ++kr) {
-            const double kk = kv[kr];
+            for (int kr = 0; kr < HK; ++kr) {
+              const double kk = kv[kr];
 #pragma unroll
-            for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
+              for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
+            }
+          }
+        } else {
+          for (int kc = 0; kc < p.wk; ++kc) {
+            double w[TI + (HK > 0 ? HK : 1) - 1];
+#pragma unroll
+            for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[min(u, last) * pitch + kc];
+            const double* kv = kflip + kc * hk_pad;
+#pragma unroll
+            for (int kr = 0; kr < HK; ++kr) {
+              const double kk = kv[kr];
+#pragma unroll
+              for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
+            }
           }
         }
       } else {
@@ -126,7 +143,7 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
             const double kk = kv[kr];
 #pragma unroll
             for (int t = 0; t < TI; ++t)
-              if (t < nt) acc[t] = fma(kk, col[(size_t)(t + kr) * pitch + kc], acc[t]);
+              if (t < nt) acc[t] = fma(kk, col[(t + kr) * pitch + kc], acc[t]);
           }
         }
       }
@@ -151,29 +168,32 @@ size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int 
 typedef void (*direct_fn)(const DirectParams);
 
 template <int HK>
-static direct_fn pick(bool tall) { return tall ? direct_kernel<HK, 8> : direct_kernel<HK, 1>; }
+static direct_fn pick(bool tall, bool wrap) {
+  if (wrap) return tall ? direct_kernel<HK, 8, true> : direct_kernel<HK, 1, true>;
+  return tall ? direct_kernel<HK, 8, false> : direct_kernel<HK, 1, false>;
+}
 
-static direct_fn direct_variant(int hk, int hd) {
+static direct_fn direct_variant(int hk, int hd, bool wrap) {
   const bool tall = hd >= 8;
   switch (hk) {
-    case 1: return pick<1>(tall);   case 2: return pick<2>(tall);   case 3: return pick<3>(tall);   case 4: return pick<4>(tall);
-    case 5: return pick<5>(tall);   case 6: return pick<6>(tall);   case 7: return pick<7>(tall);   case 8: return pick<8>(tall);
-    case 9: return pick<9>(tall);   case 10: return pick<10>(tall); case 11: return pick<11>(tall); case 12: return pick<12>(tall);
-    case 13: return pick<13>(tall); case 14: return pick<14>(tall); case 15: return pick<15>(tall); case 16: return pick<16>(tall);
+    case 1: return pick<1>(tall, wrap);   case 2: return pick<2>(tall, wrap);   case 3: return pick<3>(tall, wrap);   case 4: return pick<4>(tall, wrap);
+    case 5: return pick<5>(tall, wrap);   case 6: return pick<6>(tall, wrap);   case 7: return pick<7>(tall, wrap);   case 8: return pick<8>(tall, wrap);
+    case 9: return pick<9>(tall, wrap);   case 10: return pick<10>(tall, wrap); case 11: return pick<11>(tall, wrap); case 12: return pick<12>(tall, wrap);
+    case 13: return pick<13>(tall, wrap); case 14: return pick<14>(tall, wrap); case 15: return pick<15>(tall, wrap); case 16: return pick<16>(tall, wrap);
   }
-  return pick<0>(tall);
+  return pick<0>(tall, wrap);
 }
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
-  direct_fn fn = direct_variant(p.hk, p.hd);
+  direct_fn fn = direct_variant(p.hk, p.hd, p.wrap_h > 0);
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   fn<<<grid, kDirectThreads, smem, st>>>(p);
   return cudaGetLastError();
 }
 
-int occupancy_direct(int hk, int hd, size_t smem) {
+int occupancy_direct(int hk, int hd, bool wrap, size_t smem) {
   int n = 0;
-  direct_fn fn = direct_variant(hk, hd);
+  direct_fn fn = direct_variant(hk, hd, wrap);
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
   return n;
