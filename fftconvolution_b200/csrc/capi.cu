@@ -204,8 +204,8 @@ size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (si
 
 // Crossover between the direct kernel and the FFT chain: two time models per image, fitted to the
 // measured sweep profiles/r01_crossover.csv (tools/crossover_sweep.py).
-//   direct: max(HBM stream at 3.0 TB/s (2.3 below 64 rows), FMAs at 4.8 TFMA/s) for the 8-rows-per-thread variant,
-//           HBM at 2.5 TB/s + FMAs at 3.1 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image
+//   direct: max(HBM stream at 3.5 TB/s (2.8 below 64 rows), FMAs at 5.2 TFMA/s) for the 8-rows-per-thread variant,
+//           HBM at 3.4 TB/s + FMAs at 4.5 TFMA/s for the 1-row variant (1-D signals), + 4 ns per image
 //           (0.4 ns with a shared kernel: small images are processed in groups per CTA);
 //           kernels taller than 16 rows run a general variant that is about 4x slower.
 //   FFT   : planner cost units x 0.15 ps, never below 10 ns per image (generic kernel); 5.6-6.5 ps per point
@@ -215,8 +215,8 @@ int auto_path(const Plan2D& pl, bool shared) {
   const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
   double t_direct;
   const double per_image = shared ? 0.4e-9 : 4e-9;
-  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / (pl.h.n_dst >= 64 ? 3.0e12 : 2.3e12), fma / 4.8e12) + per_image;
-  else t_direct = bytes / 2.5e12 + fma / 3.1e12 + per_image;
+  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / (pl.h.n_dst >= 64 ? 3.5e12 : 2.8e12), fma / 5.2e12) + per_image;
+  else t_direct = bytes / 3.4e12 + fma / 4.5e12 + per_image;
   if (pl.h.n_ker > 16) t_direct *= 4.0;
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;

@@ -63,33 +63,62 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
     const int cols = p.wd + p.wk - 1;
     const int nelem = rows * pitch;            // staged doubles per image
     const int nall = ng * nelem;
-    // Each thread walks the staged elements idx = tid, tid + 256, ... keeping (image g, row u, column v)
-    // by increments (no division per element); eight independent global loads are in flight per thread.
-    const int step_u = kDirectThreads / pitch, step_v = kDirectThreads - step_u * pitch;   // 256 = step_u * pitch + step_v
-    int u = threadIdx.x / pitch, v = threadIdx.x - u * pitch, g = 0;
-    if (group > 1) { g = u / rows; u -= g * rows; }
+    constexpr int SU = 8;   // independent global loads in flight per thread before the first shared store
     const int sr0 = i0 + p.off_h - (hk - 1), sc0 = p.off_w - (p.wk - 1);
-    constexpr int SU = 8;
-    for (int base = threadIdx.x; base < nall; base += SU * kDirectThreads) {
-      double vals[SU];
+    const int step_u = kDirectThreads / pitch, step_v = kDirectThreads - step_u * pitch;   // 256 = step_u * pitch + step_v
+    if (group > 1 && 2 * step_u > rows) {
+      // several very small images: flat index -> (image, row, column) by exact float-reciprocal divisions
+      const float inv_pitch = 1.0f / (float)pitch, inv_nelem = 1.0f / (float)nelem;
+      for (int base = threadIdx.x; base < nall; base += SU * kDirectThreads) {
+        double vals[SU];
 #pragma unroll
-      for (int k = 0; k < SU; ++k) {
-        double val = 0.0;
-        if (base + k * kDirectThreads < nall) {
-          int sr = sr0 + u, sc = sc0 + v;
-          if (WRAP) { sr = wrap_index(sr, p.wrap_h); sc = wrap_index(sc, p.wrap_w); }
-          if (v < cols && (unsigned)sr < (unsigned)p.hs && (unsigned)sc < (unsigned)p.ws)
-            val = __ldg(a + ((long)g * (long)src_sz + (long)(sr * p.ws + sc)));
+        for (int k = 0; k < SU; ++k) {
+          const int idx = base + k * kDirectThreads;
+          double val = 0.0;
+          if (idx < nall) {
+            const int g = fast_div(idx, nelem, inv_nelem);
+            const int rem = idx - g * nelem;
+            const int u = fast_div(rem, pitch, inv_pitch), v = rem - u * pitch;
+            int sr = sr0 + u, sc = sc0 + v;
+            if (WRAP) { sr = wrap_index(sr, p.wrap_h); sc = wrap_index(sc, p.wrap_w); }
+            if (v < cols && (unsigned)sr < (unsigned)p.hs && (unsigned)sc < (unsigned)p.ws)
+              val = __ldg(a + ((long)g * (long)src_sz + (long)(sr * p.ws + sc)));
+          }
+          vals[k] = val;
         }
-        vals[k] = val;
-        v += step_v; u += step_u;
-        if (v >= pitch) { v -= pitch; ++u; }
-        if (group > 1) { while (u >= rows) { u -= rows; ++g; } }
-      }
 #pragma unroll
-      for (int k = 0; k < SU; ++k) {
-        const int idx = base + k * kDirectThreads;
-        if (idx < nall) S[idx] = vals[k];
+        for (int k = 0; k < SU; ++k) {
+          const int idx = base + k * kDirectThreads;
+          if (idx < nall) S[idx] = vals[k];
+        }
+      }
+    } else {
+      // each thread walks idx = tid, tid + 256, ... keeping (image g, row u, column v) by increments
+      // (no division per element: the flat-index form made the kernel issue-bound)
+      int u = threadIdx.x / pitch, v = threadIdx.x - u * pitch;
+      const double* ag = a;
+      if (group > 1) { const int g0 = u / rows; u -= g0 * rows; ag += (size_t)g0 * src_sz; }
+      for (int base = threadIdx.x; base < nall; base += SU * kDirectThreads) {
+        double vals[SU];
+#pragma unroll
+        for (int k = 0; k < SU; ++k) {
+          double val = 0.0;
+          if (base + k * kDirectThreads < nall) {
+            int sr = sr0 + u, sc = sc0 + v;
+            if (WRAP) { sr = wrap_index(sr, p.wrap_h); sc = wrap_index(sc, p.wrap_w); }
+            if (v < cols && (unsigned)sr < (unsigned)p.hs && (unsigned)sc < (unsigned)p.ws)
+              val = __ldg(ag + (sr * p.ws + sc));
+          }
+          vals[k] = val;
+          v += step_v; u += step_u;
+          if (v >= pitch) { v -= pitch; ++u; }
+          if (group > 1 && u >= rows) { u -= rows; ag += src_sz; }   // 2 * step_u <= rows: at most one image per step
+        }
+#pragma unroll
+        for (int k = 0; k < SU; ++k) {
+          const int idx = base + k * kDirectThreads;
+          if (idx < nall) S[idx] = vals[k];
+        }
       }
     }
     __syncthreads();
@@ -108,31 +137,18 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
       const double* col = S + (g * nelem + r0 * pitch + j);       // 32-bit offsets into shared memory
       if (HK > 0) {
         const int last = rows - 1 - r0;   // highest staged row of this window (rows past it feed no existing output)
-        if (last >= TI + HK - 2) {        // whole window staged: no clamping
-          for (int kc = 0; kc < p.wk; ++kc) {
-            double w[TI + (HK > 0 ? HK : 1) - 1];
+        // (a clamp-free copy of this loop for windows that are fully staged measured slower: lanes of a warp
+        // straddle both cases and run both)
+        for (int kc = 0; kc < p.wk; ++kc) {
+          double w[TI + (HK > 0 ? HK : 1) - 1];
 #pragma unroll
-            for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[u * pitch + kc];
-            const double* kv = kflip + kc * hk_pad;
+          for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[min(u, last) * pitch + kc];
+          const double* kv = kflip + kc * hk_pad;
 #pragma unroll
-            for (int kr = 0; kr < HK; ++kr) {
-              const double kk = kv[kr];
+          for (int kr = 0; kr < HK; ++kr) {
+            const double kk = kv[kr];
 #pragma unroll
-              for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
-            }
-          }
-        } else {
-          for (int kc = 0; kc < p.wk; ++kc) {
-            double w[TI + (HK > 0 ? HK : 1) - 1];
-#pragma unroll
-            for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[min(u, last) * pitch + kc];
-            const double* kv = kflip + kc * hk_pad;
-#pragma unroll
-            for (int kr = 0; kr < HK; ++kr) {
-              const double kk = kv[kr];
-#pragma unroll
-              for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
-            }
+            for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
           }
         }
       } else {

@@ -5,7 +5,7 @@ import numpy as np, torch, fftconvolution_b200 as b2c
 torch.cuda.set_device(0)
 st = torch.cuda.current_stream().cuda_stream
 PEAK = 6540.2e9
-for (mode, hs, ws, hk, wk) in [(2, 100, 100, 1, 1), (2, 100, 100, 3, 3), (2, 100, 100, 5, 5), (2, 100, 100, 7, 7), (2, 70, 70, 3, 3), (2, 50, 50, 3, 3), (2, 50, 50, 5, 5), (2, 30, 30, 3, 3), (2, 10, 10, 3, 3), (4, 50, 50, 5, 5), (2, 1, 64, 1, 15), (2, 1, 4096, 1, 3), (2, 1, 4096, 1, 15)]:
+for (mode, hs, ws, hk, wk) in [(2, 100, 100, 1, 1), (2, 100, 100, 3, 3), (2, 100, 100, 5, 5), (2, 100, 100, 7, 7), (2, 70, 70, 3, 3), (2, 50, 50, 3, 3), (2, 50, 50, 5, 5), (2, 30, 30, 3, 3), (2, 20, 20, 7, 7), (2, 10, 10, 9, 9), (2, 10, 10, 3, 3), (4, 50, 50, 5, 5), (2, 1, 64, 1, 15), (2, 1, 4096, 1, 3), (2, 1, 4096, 1, 15)]:
     n = max(16384, min(1 << 20, (1 << 28) // (8 * hs * ws)))
     p = b2c.Plan(mode, hs, ws, hk, wk); p.set_path(b2c.PATH_DIRECT)
     src = torch.empty((n, hs, ws), dtype=torch.float64, device="cuda"); b2c.fill_uniform_device(src.data_ptr(), src.numel(), 5)
