@@ -38,8 +38,10 @@ bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, in
 cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 int big2ds_ctas_per_sm();
 bool tuned1d_has(int P);
+size_t tuned1d_scratch_elems(int P);
 cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, const double* d_src, const double* d_ker,
-                           double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
+                           double* d_dst, long n, cplx* scratch, int build_table, const cplx* tw, int sms,
+                           cudaStream_t st, int* launches);
 // conv_tuned108.cu
 size_t tuned108_smem_bytes();
 size_t tuned108_kspec_bytes();
@@ -165,11 +167,13 @@ struct b2c_plan {
   // (coalesced lanes), reported back in the caller's orientation
   bool transposed = false;
   int forced_path = B2C_PATH_AUTO;
+  bool t1d_tables = false;   // conv_tuned1d.cu: the per-pass twiddle tables behind the kernel spectrum are filled
   bool strip_only = false;   // too large for the any-size kernel: B2C_PATH_FFT_GENERIC is refused
   // lazily created device state (one device per plan)
   DeviceCtx* ctx = nullptr;
   AxisTables th, tw;
   cplx* kspec = nullptr;
+  size_t kspec_bytes = 0;
   cplx* work = nullptr;
   size_t work_slabs = 0;
   size_t work_slab_bytes = 0;
@@ -209,7 +213,7 @@ size_t work_bytes(const Plan2D& pl) { return sizeof(cplx) * (size_t)pl.h.P * (si
 //           (0.4 ns with a shared kernel: small images are processed in groups per CTA);
 //           kernels taller than 16 rows run a general variant that is about 4x slower.
 //   FFT   : planner cost units x 0.15 ps, never below 10 ns per image (generic kernel); 5.6-6.5 ps per point
-//           of the period + 1 ns for the tuned square-period kernels; 9.5 ps per point for the tuned 1-D kernels.
+//           of the period + 1 ns for the tuned square-period kernels; 6.3 ps per point for the tuned 1-D kernels.
 int auto_path(const Plan2D& pl, bool shared) {
   const double fma = (double)pl.h.n_dst * pl.w.n_dst * pl.h.n_ker * pl.w.n_ker;
   const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
@@ -225,11 +229,11 @@ int auto_path(const Plan2D& pl, bool shared) {
                      pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
   // tuned kernels: 5.6 ps (P <= 80) or 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 1 ns
   const double pp = (double)pl.h.P * pl.w.P;
-  // tuned 1-D kernels (conv_tuned1d.cu): 9.5 ps per point of the period
+  // tuned 1-D kernels (conv_tuned1d.cu): 6.3 ps per point of the period
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
                       pl.w.fold == 0 && pl.w.kwrap == pl.w.P && pl.w.n_ker <= pl.w.P;
   const double t_fft = tuned    ? (pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.0e-9
-                       : tuned1 ? 9.5e-12 * pl.w.P + 0.5e-9
+                       : tuned1 ? 6.3e-12 * pl.w.P + 0.3e-9
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
   int spw;
@@ -263,6 +267,17 @@ void fill_axis(AxisDev& d, const AxisPlan& a, const AxisTables& t) {
   d.posf = t.posf;
 }
 
+// The plan's kernel-spectrum scratch (layout depends on the path that runs); grown on demand, and whatever a
+// path cached in it is forgotten when it moves.
+int ensure_kspec(b2c_plan* p, size_t bytes) {
+  if (p->kspec && p->kspec_bytes >= bytes) return 0;
+  if (p->kspec) CUDA_TRY(cudaFree(p->kspec));
+  p->kspec = nullptr; p->kspec_bytes = 0; p->kspec_cached = false; p->t1d_tables = false;
+  CUDA_TRY(cudaMalloc(&p->kspec, bytes));
+  p->kspec_bytes = bytes;
+  return 0;
+}
+
 // Shared-kernel plans whose periods are 108 x 108 run on the tuned kernel (conv_tuned108.cu).
 bool tuned108_applies(const b2c_plan* p, int shared) {
   const Plan2D& pl = p->pl;
@@ -272,7 +287,7 @@ bool tuned108_applies(const b2c_plan* p, int shared) {
 
 int run_tuned108(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
   const Plan2D& pl = p->pl;
-  if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, work_bytes(pl)));
+  if (int rc = ensure_kspec(p, work_bytes(pl))) return rc;
   if (!p->kspec_reuse) {
     CUDA_TRY(launch_tuned108_kspec(d_ker, pl.h.n_ker, pl.w.n_ker, p->tw.tw, p->kspec, st));
     ++g_launches;
@@ -393,7 +408,7 @@ bool tuned2_applies(const b2c_plan* p, int shared) {
 
 int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
   const Plan2D& pl = p->pl;
-  if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, std::max(work_bytes(pl), tuned2_kspec_bytes(pl.h.P))));
+  if (int rc = ensure_kspec(p, std::max(work_bytes(pl), tuned2_kspec_bytes(pl.h.P)))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_timer.on && g_timer.ev.size() < 8192) {
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
@@ -417,7 +432,7 @@ bool tuned1d_applies(const b2c_plan* p, int shared) {
 
 int run_tuned1d(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
   const Plan2D& pl = p->pl;
-  if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, std::max(work_bytes(pl), sizeof(cplx) * (size_t)pl.w.P)));
+  if (int rc = ensure_kspec(p, std::max(work_bytes(pl), sizeof(cplx) * tuned1d_scratch_elems(pl.w.P)))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_timer.on && g_timer.ev.size() < 8192) {
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
@@ -425,7 +440,8 @@ int run_tuned1d(b2c_plan* p, const double* d_src, const double* d_ker, double* d
   }
   int launches = 0;
   CUDA_TRY(launch_tuned1d(pl.w.P, pl.w.n_src, pl.w.n_ker, pl.w.n_dst, pl.w.off, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n, p->kspec,
-                          p->tw.tw, p->ctx->sms, st, &launches));
+                          p->t1d_tables ? 0 : 1, p->tw.tw, p->ctx->sms, st, &launches));
+  p->t1d_tables = true;
   g_launches += launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
   return 0;
@@ -473,7 +489,7 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
   }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (shared) {
-    if (!p->kspec) CUDA_TRY(cudaMalloc(&p->kspec, wb));
+    if (int rc = ensure_kspec(p, wb)) return rc;
     q.kspec = p->kspec;
     if (!p->kspec_reuse) {
       CUDA_TRY(launch_kspec(q, 512, wb, st));
@@ -712,6 +728,7 @@ int b2c_plan_set_path(b2c_plan* p, int path) {
     return fail(B2C_ESIZE, "b2c_plan_set_path: a transform this large only runs in strip mode");
   p->forced_path = path;
   p->kspec_cached = false;   // another path keeps its spectrum in another layout
+  p->t1d_tables = false;
   return 0;
 }
 

@@ -30,8 +30,9 @@ struct Params {
   const double* src;        // [n][ns]
   double* dst;              // [n][nd]
   long n_signals;
-  const cplx* kspec;        // [P], scrambled order, scaled by 1/P
+  const cplx* kspec;        // [LAST][P / LAST]: spectrum at scrambled position b * LAST + q in entry [q][b], scaled by 1/P
   const cplx* tw;           // exp(-2 pi i k / P)
+  const cplx* twtab;        // per-pass twiddle tables [q-1][j] (lanes read consecutive entries), see Geo::OFF*
 };
 
 template <int P, int R0, int R1, int R2, int R3>
@@ -49,6 +50,12 @@ struct Geo {
   static constexpr size_t smem_bytes = sizeof(cplx) * (size_t)SLOTS;
   static __host__ __device__ constexpr int pad(int p) { return p + p / LAST; }
   static constexpr int MIN_CTAS = 2 * smem_bytes <= 225 * 1024 ? 2 : 1;   // register budget follows the CTAs that fit
+  // Twiddle tables, one per pass that has twiddles: entry (q-1) * M + j = w_N^(j*q).  Reading tw[j*q*TSTEP]
+  // instead costs one 32-byte sector per lane (ncu: L1TEX 83 % busy, long-scoreboard the top stall).
+  static constexpr int OFF0 = 0;
+  static constexpr int OFF1 = OFF0 + (R0 - 1) * (P / R0);
+  static constexpr int OFF2 = OFF1 + (R1 - 1) * (P / R0 / R1);
+  static constexpr int TABN = OFF2 + (NS == 4 ? (R2 - 1) * (P / R0 / R1 / R2) : 0);
 };
 
 // One pass.  N: block length of this pass, R: radix, M = N / R.  Element q of butterfly (b, j) sits
@@ -56,9 +63,10 @@ struct Geo {
 //   SRC_GLOBAL : inputs come from the two signals in global memory (first forward pass)
 //   DST_GLOBAL : outputs go to the two results in global memory, cropped (last backward pass)
 //   MULK       : M == 1: forward butterfly, multiply by the kernel spectrum, backward butterfly
-template <class G, int P, int N, int R, bool INV, bool SRC_GLOBAL, bool DST_GLOBAL, bool MULK>
+template <class G, int P, int N, int R, bool INV, bool SRC_GLOBAL, bool DST_GLOBAL, bool MULK, int TOFF>
 __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, const double* b2, double* da, double* db) {
-  constexpr int M = N / R, TSTEP = P / N;
+  constexpr int M = N / R;
+  const cplx* tab = p.twtab + (TOFF >= 0 ? TOFF : 0);
   for (int task = threadIdx.x; task < P / R; task += G::THREADS) {
     const int blk = task / M, j = task - blk * M;
     const int base = blk * N + j;
@@ -81,7 +89,7 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
       BigBfly<R>::run(v);
 #pragma unroll
       for (int q = 0; q < R; ++q) {
-        const cplx y = cmul(v[q], __ldg(p.kspec + base + q));
+        const cplx y = cmul(v[q], __ldg(p.kspec + q * (P / R) + blk));   // [q][block]: lanes read consecutive entries
         v[q] = make_double2(y.y, y.x);          // swapped: backward butterfly = forward on (im, re)
       }
       BigBfly<R>::run(v);
@@ -90,7 +98,7 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
     } else if (INV) {
       if (M > 1) {
 #pragma unroll
-        for (int q = 1; q < R; ++q) v[q] = cmulc(v[q], __ldg(p.tw + j * q * TSTEP));
+        for (int q = 1; q < R; ++q) v[q] = cmulc(v[q], __ldg(tab + (q - 1) * M + j));
       }
 #pragma unroll
       for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
@@ -101,7 +109,7 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
       BigBfly<R>::run(v);
       if (M > 1) {
 #pragma unroll
-        for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(p.tw + j * q * TSTEP));
+        for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(tab + (q - 1) * M + j));
       }
     }
     if (DST_GLOBAL) {
@@ -123,15 +131,15 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
 template <int P, int R0, int R1, int R2, int R3>
 __device__ __forceinline__ void forward_all_but_last(cplx* W, const Params& p, const double* a, const double* b2) {
   typedef Geo<P, R0, R1, R2, R3> G;
-  pass<G, P, P, R0, false, true, false, false>(W, p, a, b2, nullptr, nullptr);
+  pass<G, P, P, R0, false, true, false, false, G::OFF0>(W, p, a, b2, nullptr, nullptr);
   __syncthreads();
   if (G::NS == 4) {
-    pass<G, P, P / R0, R1, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    pass<G, P, P / R0, R1, false, false, false, false, G::OFF1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
-    pass<G, P, P / R0 / R1, R2, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    pass<G, P, P / R0 / R1, R2, false, false, false, false, G::OFF2>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
   } else {
-    pass<G, P, P / R0, R1, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    pass<G, P, P / R0, R1, false, false, false, false, G::OFF1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
   }
 }
@@ -148,15 +156,15 @@ __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0,
     double* da = p.dst + (size_t)(2 * pr) * p.nd;
     double* db = two ? da + p.nd : nullptr;
     forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2);
-    pass<G, P, G::LAST, G::LAST, false, false, false, true>(W, p, nullptr, nullptr, nullptr, nullptr);
+    pass<G, P, G::LAST, G::LAST, false, false, false, true, -1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
     if (G::NS == 4) {
-      pass<G, P, P / R0 / R1, R2, true, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+      pass<G, P, P / R0 / R1, R2, true, false, false, false, G::OFF2>(W, p, nullptr, nullptr, nullptr, nullptr);
       __syncthreads();
     }
-    pass<G, P, P / R0, R1, true, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+    pass<G, P, P / R0, R1, true, false, false, false, G::OFF1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
-    pass<G, P, P, R0, true, false, true, false>(W, p, nullptr, nullptr, da, db);
+    pass<G, P, P, R0, true, false, true, false, G::OFF0>(W, p, nullptr, nullptr, da, db);
     __syncthreads();   // the next pair's first pass overwrites W
   }
 }
@@ -169,18 +177,39 @@ __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), 1) kspec_ke
   typedef Geo<P, R0, R1, R2, R3> G;
   cplx* W = reinterpret_cast<cplx*>(b2c_smem_t1);
   forward_all_but_last<P, R0, R1, R2, R3>(W, p, p.src, nullptr);
-  pass<G, P, G::LAST, G::LAST, false, false, false, false>(W, p, nullptr, nullptr, nullptr, nullptr);
+  pass<G, P, G::LAST, G::LAST, false, false, false, false, -1>(W, p, nullptr, nullptr, nullptr, nullptr);
   __syncthreads();
   const double scale = 1.0 / (double)P;
   for (int i = threadIdx.x; i < P; i += G::THREADS) {
     const cplx v = W[G::pad(i)];
-    out[i] = make_double2(v.x * scale, v.y * scale);
+    out[(i % G::LAST) * (P / G::LAST) + i / G::LAST] = make_double2(v.x * scale, v.y * scale);   // position b*LAST + q -> [q][b]
+  }
+}
+
+// Fill the per-pass twiddle tables from the plan's root table (once per plan).
+template <int P, int R0, int R1, int R2, int R3>
+__global__ void twtab_kernel(const cplx* __restrict__ tw, cplx* __restrict__ tab) {
+  typedef Geo<P, R0, R1, R2, R3> G;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < G::TABN; i += gridDim.x * blockDim.x) {
+    int off, m, tstep;   // table of the pass with block length N = P / tstep, M = N / radix
+    if (i < G::OFF1) { off = G::OFF0; m = P / R0; tstep = 1; }
+    else if (i < G::OFF2) { off = G::OFF1; m = P / R0 / R1; tstep = R0; }
+    else { off = G::OFF2; m = P / R0 / R1 / R2; tstep = R0 * R1; }
+    const int k = i - off, q = k / m + 1, j = k - (q - 1) * m;
+    tab[i] = tw[j * q * tstep];
   }
 }
 
 template <int P, int R0, int R1, int R2, int R3>
-cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int sms, cudaStream_t st, int* launches) {
+cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int build_table, int sms, cudaStream_t st,
+                int* launches) {
   typedef Geo<P, R0, R1, R2, R3> G;
+  if (build_table) {
+    twtab_kernel<P, R0, R1, R2, R3><<<(G::TABN + 255) / 256, 256, 0, st>>>(p.tw, const_cast<cplx*>(p.twtab));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    ++*launches;
+  }
   auto kk = kspec_kernel<P, R0, R1, R2, R3>;
   auto ck = conv_kernel<P, R0, R1, R2, R3>;
   cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
@@ -222,13 +251,19 @@ bool tuned1d_has(int P) {
   return false;
 }
 
-// kernel spectrum + convolution for a 1-D period P from the menu; *launches += 2
+// Scratch of a 1-D plan, in complex elements: the kernel spectrum [P] followed by the twiddle tables (< 3 P).
+size_t tuned1d_scratch_elems(int P) { return (size_t)4 * P; }
+
+// (twiddle tables once per plan) + kernel spectrum + convolution for a 1-D period P from the menu
 cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, const double* d_src, const double* d_ker,
-                           double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches) {
+                           double* d_dst, long n, cplx* scratch, int build_table, const cplx* tw, int sms,
+                           cudaStream_t st, int* launches) {
   t1::Params p;
+  cplx* kspec = scratch;
   p.ns = ns; p.nd = nd; p.off = off; p.src = d_src; p.dst = d_dst; p.n_signals = n; p.kspec = kspec; p.tw = tw;
+  p.twtab = scratch + P;
   switch (P) {
-#define X(pp, a, b, c, d) case pp: return t1::run<pp, a, b, c, d>(p, d_ker, nk, kspec, sms, st, launches);
+#define X(pp, a, b, c, d) case pp: return t1::run<pp, a, b, c, d>(p, d_ker, nk, kspec, build_table, sms, st, launches);
     B2C_T1_MENU(X)
 #undef X
   }
