@@ -25,6 +25,10 @@ extern __shared__ __align__(16) unsigned char b2c_smem_t1[];
 
 namespace t1 {
 
+#ifndef B2C_T1_POW
+#define B2C_T1_POW 1
+#endif
+
 struct Params {
   int ns, nd, off;          // signal length, result length, crop offset
   const double* src;        // [n][ns]
@@ -64,8 +68,13 @@ struct Geo {
 //   DST_GLOBAL : outputs go to the two results in global memory, cropped (last backward pass)
 //   MULK       : M == 1: forward butterfly, multiply by the kernel spectrum, backward butterfly
 template <class G, int P, int N, int R, bool INV, bool SRC_GLOBAL, bool DST_GLOBAL, bool MULK, int TOFF>
-__device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, const double* b2, double* da, double* db) {
+__device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, const double* b2, double* da, double* db,
+                                     cplx wj = make_double2(1.0, 0.0)) {
   constexpr int M = N / R;
+  // first / last pass with one butterfly per thread: the thread's j never changes, its root w_P^j lives in
+  // registers and the R-1 twiddles are its powers (17 dependent multiplications cost less than 17 table
+  // reads that together move as many bytes through L2 as the signals themselves)
+  constexpr bool POW = B2C_T1_POW && N == P && (P / R <= G::THREADS) && R <= 16;   // radix 18 and 20 spill with it
   const cplx* tab = p.twtab + (TOFF >= 0 ? TOFF : 0);
   for (int task = threadIdx.x; task < P / R; task += G::THREADS) {
     const int blk = task / M, j = task - blk * M;
@@ -97,8 +106,14 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
       for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
     } else if (INV) {
       if (M > 1) {
+        if (POW) {   // w^(j*q) by repeated multiplication from the thread's own w^j (see conv_kernel)
+          cplx cur = wj;
 #pragma unroll
-        for (int q = 1; q < R; ++q) v[q] = cmulc(v[q], __ldg(tab + (q - 1) * M + j));
+          for (int q = 1; q < R; ++q) { v[q] = cmulc(v[q], cur); cur = cmul(cur, wj); }
+        } else {
+#pragma unroll
+          for (int q = 1; q < R; ++q) v[q] = cmulc(v[q], __ldg(tab + (q - 1) * M + j));
+        }
       }
 #pragma unroll
       for (int q = 0; q < R; ++q) v[q] = cswap(v[q]);
@@ -108,8 +123,14 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
     } else {
       BigBfly<R>::run(v);
       if (M > 1) {
+        if (POW) {
+          cplx cur = wj;
 #pragma unroll
-        for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(tab + (q - 1) * M + j));
+          for (int q = 1; q < R; ++q) { v[q] = cmul(v[q], cur); cur = cmul(cur, wj); }
+        } else {
+#pragma unroll
+          for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(tab + (q - 1) * M + j));
+        }
       }
     }
     if (DST_GLOBAL) {
@@ -129,9 +150,9 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
 }
 
 template <int P, int R0, int R1, int R2, int R3>
-__device__ __forceinline__ void forward_all_but_last(cplx* W, const Params& p, const double* a, const double* b2) {
+__device__ __forceinline__ void forward_all_but_last(cplx* W, const Params& p, const double* a, const double* b2, cplx wj) {
   typedef Geo<P, R0, R1, R2, R3> G;
-  pass<G, P, P, R0, false, true, false, false, G::OFF0>(W, p, a, b2, nullptr, nullptr);
+  pass<G, P, P, R0, false, true, false, false, G::OFF0>(W, p, a, b2, nullptr, nullptr, wj);
   __syncthreads();
   if (G::NS == 4) {
     pass<G, P, P / R0, R1, false, false, false, false, G::OFF1>(W, p, nullptr, nullptr, nullptr, nullptr);
@@ -149,13 +170,14 @@ __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0,
   typedef Geo<P, R0, R1, R2, R3> G;
   cplx* W = reinterpret_cast<cplx*>(b2c_smem_t1);
   const long pairs = (p.n_signals + 1) / 2;
+  const cplx wj = __ldg(p.tw + (threadIdx.x < P / R0 ? threadIdx.x : 0));   // w_P^j of this thread's first-pass butterfly
   for (long pr = blockIdx.x; pr < pairs; pr += gridDim.x) {
     const double* a = p.src + (size_t)(2 * pr) * p.ns;
     const bool two = 2 * pr + 1 < p.n_signals;
     const double* b2 = two ? a + p.ns : nullptr;
     double* da = p.dst + (size_t)(2 * pr) * p.nd;
     double* db = two ? da + p.nd : nullptr;
-    forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2);
+    forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2, wj);
     pass<G, P, G::LAST, G::LAST, false, false, false, true, -1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
     if (G::NS == 4) {
@@ -164,7 +186,7 @@ __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0,
     }
     pass<G, P, P / R0, R1, true, false, false, false, G::OFF1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
-    pass<G, P, P, R0, true, false, true, false, G::OFF0>(W, p, nullptr, nullptr, da, db);
+    pass<G, P, P, R0, true, false, true, false, G::OFF0>(W, p, nullptr, nullptr, da, db, wj);
     __syncthreads();   // the next pair's first pass overwrites W
   }
 }
@@ -176,7 +198,7 @@ template <int P, int R0, int R1, int R2, int R3>
 __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), 1) kspec_kernel(const __grid_constant__ Params p, cplx* out) {
   typedef Geo<P, R0, R1, R2, R3> G;
   cplx* W = reinterpret_cast<cplx*>(b2c_smem_t1);
-  forward_all_but_last<P, R0, R1, R2, R3>(W, p, p.src, nullptr);
+  forward_all_but_last<P, R0, R1, R2, R3>(W, p, p.src, nullptr, __ldg(p.tw + (threadIdx.x < P / R0 ? threadIdx.x : 0)));
   pass<G, P, G::LAST, G::LAST, false, false, false, false, -1>(W, p, nullptr, nullptr, nullptr, nullptr);
   __syncthreads();
   const double scale = 1.0 / (double)P;
