@@ -220,7 +220,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   double t_direct;
   const double per_image = shared ? 0.4e-9 : 4e-9;
   if (pl.h.n_dst >= 8) t_direct = std::max(bytes / (pl.h.n_dst >= 64 ? 3.5e12 : 2.8e12), fma / 5.2e12) + per_image;
-  else t_direct = bytes / 3.4e12 + fma / 4.5e12 + per_image;
+  else t_direct = bytes / 3.4e12 + fma / 4.5e12 + (shared ? std::min(2e-9, bytes * 1.25e-13) : per_image);   // long rows: one tile per CTA
   if (pl.h.n_ker > 16) t_direct *= 4.0;
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
