@@ -231,7 +231,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   const double pp = (double)pl.h.P * pl.w.P;
   // tuned 1-D kernels (conv_tuned1d.cu): 6.3 ps per point of the period
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
-                      pl.w.fold == 0 && pl.w.kwrap == pl.w.P && pl.w.n_ker <= pl.w.P;
+                      pl.w.fold == 0 && pl.w.kwrap == pl.w.P;
   const double t_fft = tuned    ? (pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.0e-9
                        : tuned1 ? 6.3e-12 * pl.w.P + 0.3e-9
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
@@ -427,7 +427,7 @@ int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_
 bool tuned1d_applies(const b2c_plan* p, int shared) {
   const Plan2D& pl = p->pl;
   return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 &&
-         tuned1d_has(pl.w.P) && pl.w.fold == 0 && pl.w.kwrap == pl.w.P && pl.w.n_ker <= pl.w.P;
+         tuned1d_has(pl.w.P) && pl.w.fold == 0 && pl.w.kwrap == pl.w.P;   // a longer kernel wraps in the spectrum kernel
 }
 
 int run_tuned1d(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {

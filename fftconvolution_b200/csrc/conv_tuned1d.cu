@@ -85,9 +85,11 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
       for (int q = 0; q < R; ++q) {
         const int pos = base + M * q;
         v[q] = make_double2(0.0, 0.0);
-        if (pos < p.ns) {
-          v[q].x = __ldg(a + pos);
-          if (b2) v[q].y = __ldg(b2 + pos);
+        // samples congruent modulo the period add up (a kernel longer than the period, convolution_fftw.h:185-187);
+        // a signal never is, so this is one iteration
+        for (int i = pos; i < p.ns; i += P) {
+          v[q].x += __ldg(a + i);
+          if (b2) v[q].y += __ldg(b2 + i);
         }
       }
     } else {
@@ -259,6 +261,7 @@ cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int b
 
 // ---- the menu: (P, R0, R1, R2, R3); the planner prefers these periods for 1-D signals ------------
 #define B2C_T1_MENU(X)                                                                                          \
+  X(128, 4, 4, 8, 1) X(192, 4, 6, 8, 1) X(256, 4, 8, 8, 1) X(320, 5, 8, 8, 1) X(384, 6, 8, 8, 1)                  \
   X(512, 8, 8, 8, 1) X(640, 8, 8, 10, 1) X(768, 8, 8, 12, 1) X(1024, 8, 8, 16, 1) X(1280, 8, 10, 16, 1)         \
   X(1536, 8, 12, 16, 1) X(2048, 8, 16, 16, 1) X(2304, 9, 16, 16, 1) X(2560, 10, 16, 16, 1) X(3072, 12, 16, 16, 1) \
   X(4096, 16, 16, 16, 1) X(4608, 18, 16, 16, 1) X(5120, 20, 16, 16, 1) X(6144, 8, 8, 8, 12) X(8192, 8, 8, 8, 16)

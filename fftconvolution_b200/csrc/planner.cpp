@@ -219,7 +219,7 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
   // 1-D row signals: periods with a tuned kernel (conv_tuned1d.cu: three or four big-radix passes instead of
   // the any-size kernel's five or more small ones, ~3x faster per point) are worth up to 60 % more points
   if (hs == 1 && hk == 1 && !out.w.exact && out.w.fold == 0) {
-    static const int menu1d[] = {512, 640, 768, 1024, 1280, 1536, 2048, 2304, 2560, 3072, 4096, 4608, 5120, 6144, 8192};
+    static const int menu1d[] = {128, 192, 256, 320, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2304, 2560, 3072, 4096, 4608, 5120, 6144, 8192};
     for (int pm : menu1d) {
       if (pm < out.w.min_period) continue;
       if (pm <= out.w.min_period + (out.w.min_period * 3) / 5) out.w.P = pm;

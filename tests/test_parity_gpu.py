@@ -224,7 +224,8 @@ def test_tuned_1d_period_family_vs_oracle(b2c, oracle, torch_cuda):
     the oracle and against the any-size kernel."""
     torch = torch_cuda
     rng = np.random.default_rng(53)
-    cases = [(2, 480, 64, 512), (0, 600, 41, 640), (3, 768, 100, 768), (2, 1000, 40, 1024), (0, 1000, 255, 1280), (5, 1200, 300, 1536),
+    cases = [(2, 100, 40, 128), (0, 150, 30, 192), (2, 63, 255, 192), (3, 256, 100, 256), (2, 300, 33, 320), (0, 301, 70, 384),
+             (2, 480, 64, 512), (0, 600, 41, 640), (3, 768, 100, 768), (2, 1000, 40, 1024), (0, 1000, 255, 1280), (5, 1200, 300, 1536),
              (2, 2000, 64, 2048), (0, 2100, 200, 2304), (2, 2500, 120, 2560), (7, 3000, 73, 3072), (4, 4096, 255, 4096),
              (2, 4096, 255, 4608), (0, 4096, 1000, 5120), (2, 4096, 4096, 6144), (0, 4095, 4095, 8192), (6, 4000, 97, 4096)]
     for k, (mode, ns, nk, P) in enumerate(cases):
