@@ -39,7 +39,7 @@ cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaSt
 int big2ds_ctas_per_sm();
 bool tuned1d_has(int P);
 size_t tuned1d_scratch_elems(int P);
-cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, const double* d_src, const double* d_ker,
+cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, int n_in, int shift, const double* d_src, const double* d_ker,
                            double* d_dst, long n, cplx* scratch, int build_table, const cplx* tw, int sms,
                            cudaStream_t st, int* launches);
 // conv_tuned108.cu
@@ -53,8 +53,8 @@ cudaError_t launch_tuned108_conv(int hs, int ws, int hd, int wd, int off_h, int 
 bool tuned2_has(int P);
 size_t tuned2_kspec_bytes(int P);
 cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
-                          const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kspec,
-                          const cplx* tw, int sms, cudaStream_t st, int* launches);
+                          int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker,
+                          double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
 // util_kernels.cu
 cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long first, cudaStream_t st);
 cudaError_t launch_checksum(const double* d, long n, unsigned long long* d_out3, cudaStream_t st);
@@ -166,6 +166,11 @@ struct b2c_plan {
   // an N x 1 column signal has the memory layout of a 1 x N row signal: planned and run as a row
   // (coalesced lanes), reported back in the caller's orientation
   bool transposed = false;
+  // CIRCULAR_SAME whose own period has no tuned kernel: the periodic-extension form at a menu period
+  // (planner.h make_plan_circular_ext), used by the tuned shared-kernel kernels only
+  bool has_ext = false;
+  Plan2D ext;
+  AxisTables tw_ext;
   int forced_path = B2C_PATH_AUTO;
   bool t1d_tables = false;   // conv_tuned1d.cu: the per-pass twiddle tables behind the kernel spectrum are filled
   bool strip_only = false;   // too large for the any-size kernel: B2C_PATH_FFT_GENERIC is refused
@@ -254,6 +259,8 @@ int ensure_device_state(b2c_plan* p) {
   if (int rc = get_ctx(&c)) return rc;
   if (int rc = get_tables(c, p->pl.h, &p->th)) return rc;
   if (int rc = get_tables(c, p->pl.w, &p->tw)) return rc;
+  if (p->has_ext)
+    if (int rc = get_tables(c, p->ext.w, &p->tw_ext)) return rc;
   p->ctx = c;
   return 0;
 }
@@ -400,14 +407,13 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
 }
 
 // Shared-kernel plans with equal periods from the tuned menu (conv_tuned2.cu).
-bool tuned2_applies(const b2c_plan* p, int shared) {
-  const Plan2D& pl = p->pl;
+bool tuned2_applies(const b2c_plan* p, const Plan2D& pl, int shared) {
   return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == pl.w.P && tuned2_has(pl.h.P) &&
          pl.h.fold == 0 && pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
 }
 
-int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
-  const Plan2D& pl = p->pl;
+int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const double* d_src, const double* d_ker, double* d_dst, long n,
+               cudaStream_t st) {
   if (int rc = ensure_kspec(p, std::max(work_bytes(pl), tuned2_kspec_bytes(pl.h.P)))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_timer.on && g_timer.ev.size() < 8192) {
@@ -416,7 +422,8 @@ int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_
   }
   int launches = 0;
   CUDA_TRY(launch_tuned2(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
-                         pl.w.off, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n, p->kspec, p->tw.tw, p->ctx->sms, st, &launches));
+                         pl.w.off, pl.h.n_in, pl.w.n_in, pl.h.src_shift, pl.w.src_shift, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n,
+                         p->kspec, tww.tw, p->ctx->sms, st, &launches));
   g_launches += launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
   return 0;
@@ -424,14 +431,13 @@ int run_tuned2(b2c_plan* p, const double* d_src, const double* d_ker, double* d_
 
 // 1-D signals (vertical period 1) with a shared kernel and a horizontal period from the 1-D menu
 // (conv_tuned1d.cu).
-bool tuned1d_applies(const b2c_plan* p, int shared) {
-  const Plan2D& pl = p->pl;
+bool tuned1d_applies(const b2c_plan* p, const Plan2D& pl, int shared) {
   return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 &&
          tuned1d_has(pl.w.P) && pl.w.fold == 0 && pl.w.kwrap == pl.w.P;   // a longer kernel wraps in the spectrum kernel
 }
 
-int run_tuned1d(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
-  const Plan2D& pl = p->pl;
+int run_tuned1d(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const double* d_src, const double* d_ker, double* d_dst, long n,
+                cudaStream_t st) {
   if (int rc = ensure_kspec(p, std::max(work_bytes(pl), sizeof(cplx) * tuned1d_scratch_elems(pl.w.P)))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_timer.on && g_timer.ev.size() < 8192) {
@@ -439,8 +445,8 @@ int run_tuned1d(b2c_plan* p, const double* d_src, const double* d_ker, double* d
     CUDA_TRY(cudaEventRecord(e0, st));
   }
   int launches = 0;
-  CUDA_TRY(launch_tuned1d(pl.w.P, pl.w.n_src, pl.w.n_ker, pl.w.n_dst, pl.w.off, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n, p->kspec,
-                          p->t1d_tables ? 0 : 1, p->tw.tw, p->ctx->sms, st, &launches));
+  CUDA_TRY(launch_tuned1d(pl.w.P, pl.w.n_src, pl.w.n_ker, pl.w.n_dst, pl.w.off, pl.w.n_in, pl.w.src_shift, d_src,
+                          p->kspec_reuse ? nullptr : d_ker, d_dst, n, p->kspec, p->t1d_tables ? 0 : 1, tww.tw, p->ctx->sms, st, &launches));
   p->t1d_tables = true;
   g_launches += launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
@@ -451,9 +457,13 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
                  long n, cudaStream_t st) {
   if (int rc = ensure_device_state(p)) return rc;
   const Plan2D& pl = p->pl;
+  if (p->has_ext && shared && p->forced_path != B2C_PATH_FFT_GENERIC) {   // CIRCULAR_SAME on a tuned menu period
+    if (tuned2_applies(p, p->ext, shared)) return run_tuned2(p, p->ext, p->tw_ext, d_src, d_ker, d_dst, n, st);
+    if (tuned1d_applies(p, p->ext, shared)) return run_tuned1d(p, p->ext, p->tw_ext, d_src, d_ker, d_dst, n, st);
+  }
   if (tuned108_applies(p, shared)) return run_tuned108(p, d_src, d_ker, d_dst, n, st);
-  if (tuned2_applies(p, shared)) return run_tuned2(p, d_src, d_ker, d_dst, n, st);
-  if (tuned1d_applies(p, shared)) return run_tuned1d(p, d_src, d_ker, d_dst, n, st);
+  if (tuned2_applies(p, p->pl, shared)) return run_tuned2(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
+  if (tuned1d_applies(p, p->pl, shared)) return run_tuned1d(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&
       p->forced_path != B2C_PATH_FFT_GENERIC)
     return run_big2d(p, d_src, d_ker, shared, d_dst, n, st);
@@ -572,7 +582,7 @@ int effective_path(const b2c_plan* p, int shared) {
         direct_smem_bytes(pl.h.n_ker, pl.w.n_ker, pl.w.n_dst, std::min(8, pl.h.n_dst), &spw) <= 100 * 1024)
       return B2C_PATH_DIRECT;
   }
-  return auto_path(p->pl, shared != 0);
+  return auto_path((p->has_ext && shared) ? p->ext : p->pl, shared != 0);
 }
 
 void free_pipe(b2c_plan* p) {
@@ -680,6 +690,9 @@ int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kerne
     delete p;
     return fail(B2C_EINVAL, "b2c_plan_create: planning failed");
   }
+  // CIRCULAR_SAME whose own period (exact, or folded when the size is not smooth) has no tuned kernel
+  if (mode == B2C_CIRCULAR_SAME && !plan_on_tuned_menu(p->pl))
+    p->has_ext = make_plan_circular_ext(h_src, w_src, h_kernel, w_kernel, p->ext);
   if (!p->pl.empty && (long)p->pl.h.P * (long)work_ld(p->pl) >= (1L << 24)) {
     // Beyond the any-size kernel's 32-bit work-buffer offsets only strip mode runs (conv_big2d.cu):
     // it needs one row and a strip of one column pair in shared memory (227 KB) and no folding.

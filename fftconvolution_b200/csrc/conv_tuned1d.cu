@@ -31,6 +31,7 @@ namespace t1 {
 
 struct Params {
   int ns, nd, off;          // signal length, result length, crop offset
+  int n_in, shift;          // input positions and periodic-extension shift: position q holds sample (q - shift) mod ns
   const double* src;        // [n][ns]
   double* dst;              // [n][nd]
   long n_signals;
@@ -85,12 +86,21 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
       for (int q = 0; q < R; ++q) {
         const int pos = base + M * q;
         v[q] = make_double2(0.0, 0.0);
-        // samples congruent modulo the period add up (a kernel longer than the period, convolution_fftw.h:185-187);
-        // a signal never is, so this is one iteration
-        for (int i = pos; i < p.ns; i += P) {
-          v[q].x += __ldg(a + i);
-          if (b2) v[q].y += __ldg(b2 + i);
+        if (pos < p.n_in) {
+          int si = pos - p.shift;
+          if (si < 0) si += p.ns;
+          v[q].x = __ldg(a + si);
+          if (b2) v[q].y = __ldg(b2 + si);
         }
+      }
+      if (p.n_in > P) {   // samples congruent modulo the period add up (a kernel longer than the period,
+                          // convolution_fftw.h:185-187); kept out of the loads above so that they stay independent
+#pragma unroll
+        for (int q = 0; q < R; ++q)
+          for (int i = base + M * q + P; i < p.n_in; i += P) {
+            v[q].x += __ldg(a + i);
+            if (b2) v[q].y += __ldg(b2 + i);
+          }
       }
     } else {
 #pragma unroll
@@ -239,7 +249,7 @@ cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int b
   cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
   cudaFuncSetAttribute(ck, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
   Params pk = p;
-  pk.src = d_ker; pk.ns = nk; pk.n_signals = 1;
+  pk.src = d_ker; pk.ns = nk; pk.n_in = nk; pk.shift = 0; pk.n_signals = 1;
   if (d_ker) {   // nullptr: the spectrum of the previous call is still valid (single-call kernel cache)
     kk<<<1, G::THREADS, G::smem_bytes, st>>>(pk, kspec);
     cudaError_t e = cudaGetLastError();
@@ -280,12 +290,12 @@ bool tuned1d_has(int P) {
 size_t tuned1d_scratch_elems(int P) { return (size_t)4 * P; }
 
 // (twiddle tables once per plan) + kernel spectrum + convolution for a 1-D period P from the menu
-cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, const double* d_src, const double* d_ker,
+cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, int n_in, int shift, const double* d_src, const double* d_ker,
                            double* d_dst, long n, cplx* scratch, int build_table, const cplx* tw, int sms,
                            cudaStream_t st, int* launches) {
   t1::Params p;
   cplx* kspec = scratch;
-  p.ns = ns; p.nd = nd; p.off = off; p.src = d_src; p.dst = d_dst; p.n_signals = n; p.kspec = kspec; p.tw = tw;
+  p.ns = ns; p.nd = nd; p.off = off; p.n_in = n_in; p.shift = shift; p.src = d_src; p.dst = d_dst; p.n_signals = n; p.kspec = kspec; p.tw = tw;
   p.twtab = scratch + P;
   switch (P) {
 #define X(pp, a, b, c, d) case pp: return t1::run<pp, a, b, c, d>(p, d_ker, nk, kspec, build_table, sms, st, launches);

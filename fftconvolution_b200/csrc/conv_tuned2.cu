@@ -25,6 +25,9 @@ namespace t2 {
 
 struct Params {
   int hs, ws, hd, wd, off_h, off_w;
+  // periodic-extension form of CIRCULAR_SAME (planner.h): the transform input has hs_in x ws_in positions,
+  // position (r, c) holds source sample ((r - sh_h) mod hs, (c - sh_w) mod ws); hs, ws, 0, 0 otherwise
+  int hs_in, ws_in, sh_h, sh_w;
   const double* src;
   double* dst;
   long n_images;
@@ -97,15 +100,30 @@ conv_kernel(const __grid_constant__ Params p) {
     for (int rnd = 0; rnd < A_ROUNDS; ++rnd) {
       const int line = rnd * A_LINES + la;
       if (act && line < HALF) {
-        const bool c0 = line < p.ws, c1 = line + HALF < p.ws;
-        const double* xr = x + j * p.ws + line;
-        const int step = R2 * p.ws;
+        const bool c0 = line < p.ws_in, c1 = line + HALF < p.ws_in;
         cplx v[R1];
+        if ((p.sh_h | p.sh_w) == 0) {
+          const double* xr = x + j * p.ws + line;
+          const int step = R2 * p.ws;
 #pragma unroll
-        for (int q = 0; q < R1; ++q) {
-          const bool in = j + R2 * q < p.hs;
-          v[q].x = (in && c0) ? __ldg(xr + q * step) : 0.0;
-          v[q].y = (in && c1) ? __ldg(xr + q * step + HALF) : 0.0;
+          for (int q = 0; q < R1; ++q) {
+            const bool in = j + R2 * q < p.hs;
+            v[q].x = (in && c0) ? __ldg(xr + q * step) : 0.0;
+            v[q].y = (in && c1) ? __ldg(xr + q * step + HALF) : 0.0;
+          }
+        } else {   // source extended periodically by (sh_h, sh_w) samples in front
+          int sc0 = line - p.sh_w, sc1 = line + HALF - p.sh_w;
+          if (sc0 < 0) sc0 += p.ws;
+          if (sc1 < 0) sc1 += p.ws;
+#pragma unroll
+          for (int q = 0; q < R1; ++q) {
+            const int r = j + R2 * q;
+            int sr = r - p.sh_h;
+            if (sr < 0) sr += p.hs;
+            const bool in = r < p.hs_in;
+            v[q].x = (in && c0) ? __ldg(x + sr * p.ws + sc0) : 0.0;
+            v[q].y = (in && c1) ? __ldg(x + sr * p.ws + sc1) : 0.0;
+          }
         }
         Big<R1>::run(v);
         cplx* z = Z + line * LD + j;
@@ -313,7 +331,7 @@ cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, c
 // ---- the menu: square periods with a tuned kernel (108 = 12 x 9 is conv_tuned108.cu) -------------
 #define B2C_T2_MENU(X)                                                                                         \
   X(8, 2) X(10, 2) X(8, 3) X(4, 7) X(8, 4) X(6, 6) X(8, 5) X(6, 7) X(8, 6) X(10, 5) X(6, 9) X(8, 7) X(10, 6) X(8, 8) \
-  X(10, 7) X(8, 9) X(10, 8) X(12, 7) X(10, 9) X(12, 8) X(10, 10) X(14, 8) X(12, 10) X(14, 9) X(16, 8)
+  X(10, 7) X(8, 9) X(10, 8) X(12, 7) X(10, 9) X(12, 8) X(10, 10) X(12, 9) X(14, 8) X(12, 10) X(14, 9) X(16, 8)
 
 bool tuned2_has(int P) {
   switch (P) {
@@ -329,10 +347,11 @@ size_t tuned2_kspec_bytes(int P) { return sizeof(cplx) * (size_t)P * (size_t)((P
 
 // kernel spectrum + convolution for a square period P from the menu; *launches += 2
 cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
-                          const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kspec,
+                          int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kspec,
                           const cplx* tw, int sms, cudaStream_t st, int* launches) {
   t2::Params p;
   p.hs = hs; p.ws = ws; p.hd = hd; p.wd = wd; p.off_h = off_h; p.off_w = off_w;
+  p.hs_in = hs_in; p.ws_in = ws_in; p.sh_h = sh_h; p.sh_w = sh_w;
   p.src = d_src; p.dst = d_dst; p.n_images = n; p.kspec = kspec; p.tw = tw;
   switch (P) {
 #define X(a, b) case (a) * (b): return t2::run<a, b>(p, d_ker, hk, wk, sms, st, launches);

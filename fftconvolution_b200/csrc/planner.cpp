@@ -164,6 +164,58 @@ static void axis_for_mode(int mode, int ns, int nk, AxisPlan& a) {
   }
 }
 
+// Periods with a tuned shared-kernel kernel: square 2-D (conv_tuned108.cu, conv_tuned2.cu) and 1-D (conv_tuned1d.cu).
+static const int kMenu2D[] = {16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128};
+static const int kMenu1D[] = {128, 192, 256, 320, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2304, 2560, 3072, 4096, 4608, 5120, 6144, 8192};
+
+static bool in_menu(const int* menu, int n, int P) {
+  for (int i = 0; i < n; ++i)
+    if (menu[i] == P) return true;
+  return false;
+}
+
+bool plan_on_tuned_menu(const Plan2D& pl) {
+  if (pl.empty || pl.h.fold || pl.w.fold || pl.h.kwrap != pl.h.P || pl.w.kwrap != pl.w.P) return false;
+  if (pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1) return in_menu(kMenu1D, sizeof kMenu1D / sizeof kMenu1D[0], pl.w.P);
+  return pl.h.P == pl.w.P && in_menu(kMenu2D, sizeof kMenu2D / sizeof kMenu2D[0], pl.h.P);
+}
+
+static void ext_axis(AxisPlan& a, int ns, int nk, int P) {
+  a = AxisPlan();
+  a.n_src = ns; a.n_ker = nk; a.n_dst = ns;
+  a.off = nk - 1; a.src_shift = nk - 1; a.n_in = ns + nk - 1;
+  a.lin = a.min_period = ns + nk - 1;
+  a.P = P; a.kwrap = P; a.n_ker_eff = nk;
+  finish_axis(a);
+}
+
+bool make_plan_circular_ext(int hs, int ws, int hk, int wk, Plan2D& out) {
+  if (hs < 1 || ws < 1 || hk < 1 || wk < 1 || hk > hs || wk > ws) return false;
+  out = Plan2D();
+  out.mode = 4;
+  out.ref_h_fft = hs; out.ref_w_fft = ws;
+  if (hs == 1) {   // 1 x N row signal
+    const int need = ws + wk - 1;
+    for (int pm : kMenu1D) {
+      if (pm < need) continue;
+      if (pm > 2 * need) return false;
+      ext_axis(out.h, 1, 1, 1);
+      ext_axis(out.w, ws, wk, pm);
+      return true;
+    }
+    return false;
+  }
+  if (ws == 1) return false;   // columns are planned as rows by the caller
+  const int need = std::max(hs + hk - 1, ws + wk - 1);
+  for (int pm : kMenu2D) {
+    if (pm < need) continue;
+    ext_axis(out.h, hs, hk, pm);
+    ext_axis(out.w, ws, wk, pm);
+    return true;
+  }
+  return false;
+}
+
 bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
   if (mode < 0 || mode > 7) return false;
   out = Plan2D();
@@ -205,9 +257,8 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
   // square periods that have a hand-tuned kernel (conv_tuned108.cu, conv_tuned2.cu): one period for
   // both axes, about a third of the generic kernel's time at equal size (measured)
   if (!out.h.exact && !out.w.exact && out.h.fold == 0 && out.w.fold == 0 && hs > 1 && ws > 1) {
-    static const int menu[] = {16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128};
     const int need = std::max(out.h.min_period, out.w.min_period);
-    for (int pm : menu) {
+    for (int pm : kMenu2D) {
       if (pm < need) continue;
       // all tuned kernels share one seven-pass structure: their time scales with the P*P points moved,
       // anchored at 0.3 x the generic model for the measured 108 x 108 case
@@ -219,8 +270,7 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
   // 1-D row signals: periods with a tuned kernel (conv_tuned1d.cu: three or four big-radix passes instead of
   // the any-size kernel's five or more small ones, ~3x faster per point) are worth up to 60 % more points
   if (hs == 1 && hk == 1 && !out.w.exact && out.w.fold == 0) {
-    static const int menu1d[] = {128, 192, 256, 320, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2304, 2560, 3072, 4096, 4608, 5120, 6144, 8192};
-    for (int pm : menu1d) {
+    for (int pm : kMenu1D) {
       if (pm < out.w.min_period) continue;
       if (pm <= out.w.min_period + (out.w.min_period * 3) / 5) out.w.P = pm;
       break;
@@ -230,6 +280,7 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
     if (a->kwrap == 0) a->kwrap = a->P;
     a->n_ker_eff = std::min(a->n_ker, a->kwrap);
     a->lin = std::min(a->lin, a->P);
+    a->n_in = a->n_src;
     finish_axis(*a);
   }
   return true;

@@ -20,6 +20,10 @@ struct AxisPlan {
   int lin = 0;        // number of leading entries of the (periodic) linear result that are needed
   int min_period = 0; // smallest alias-safe period
   int P = 0;          // chosen 2/3/5/7-smooth period (>= min_period)
+  // Periodic-extension form of CIRCULAR_SAME (make_plan_circular_ext): the transform input has n_in = n_src +
+  // n_ker - 1 positions, position q holding source sample (q - src_shift) mod n_src; 0 / n_src otherwise
+  int src_shift = 0;
+  int n_in = 0;
   int nstages = 0;
   int radix[kMaxStages] = {0};
 };
@@ -45,6 +49,15 @@ int ref_find_closest_factor(int n);
 
 // Returns false for an unknown mode.
 bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out);
+
+// CIRCULAR_SAME as a plain linear problem: y[d] = sum_j k[j] x[(d - j) mod n] is the linear convolution of the
+// source extended periodically by n_ker - 1 samples in front, cropped at n_ker - 1 -- alias-safe at ANY period
+// >= n_src + n_ker - 1, so the tuned kernels (menu periods) can run sizes whose own period is not on a menu
+// or not even smooth.  Returns true (and the plan) only when kernel <= source on both axes and the periods
+// land on a tuned menu (square 2-D menu or 1-D menu).
+bool make_plan_circular_ext(int hs, int ws, int hk, int wk, Plan2D& out);
+// True when the periods of a plan are served by a tuned shared-kernel kernel (square / 1-D menu, no folding).
+bool plan_on_tuned_menu(const Plan2D& pl);
 
 // Position <-> frequency maps of the in-place decimation-in-frequency transform with the
 // given schedule: freq_of_pos[p] is the frequency index stored at position p after the forward

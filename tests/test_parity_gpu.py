@@ -307,6 +307,36 @@ def test_multi_device_batch_in_one_process(b2c, oracle, torch_cuda):
     torch.cuda.set_device(0)
 
 
+def test_circular_same_on_tuned_menu_periods(b2c, oracle, torch_cuda):
+    """CIRCULAR_SAME sizes whose own period has no tuned kernel (not smooth, or smooth but off the menu) run
+    as the linear convolution of the periodically extended source at a menu period (planner.h
+    make_plan_circular_ext): prime and odd sizes, rectangles, kernel == source, 1-D rows and columns, odd
+    batches -- against the oracle and against the any-size kernel (exact period or fold path)."""
+    torch = torch_cuda
+    rng = np.random.default_rng(83)
+    cases = [(31, 37, 5, 7), (97, 89, 9, 3), (45, 45, 45, 45), (63, 21, 1, 21), (100, 100, 9, 9), (50, 75, 11, 1),
+             (1, 1000, 1, 255), (1, 997, 1, 64), (613, 1, 100, 1), (1, 63, 1, 63), (1, 3000, 1, 17)]
+    for (hs, ws, hk, wk) in cases:
+        p = b2c.Plan(b2c.CIRCULAR_SAME, hs, ws, hk, wk)
+        assert (p.h_dst, p.w_dst) == (hs, ws)
+        n = 5
+        src, ker = rng.random((n, hs, ws)), rng.random((hk, wk))
+        d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+        got = {}
+        for path in (b2c.PATH_FFT, b2c.PATH_FFT_GENERIC):
+            p.set_path(path)
+            d_dst = torch.full((n, hs, ws), float("nan"), dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+            torch.cuda.synchronize()
+            got[path] = d_dst.cpu().numpy()
+        for i in (0, n - 1):
+            _check(got[b2c.PATH_FFT][i], oracle.convolve_direct8(b2c.CIRCULAR_SAME, src[i], ker), ("circular ext", hs, ws, hk, wk, i))
+        _check(got[b2c.PATH_FFT], got[b2c.PATH_FFT_GENERIC], ("circular ext vs any-size", hs, ws, hk, wk))
+        p.set_path(b2c.PATH_AUTO)
+        _check(p.convolve_host(src[1], ker), got[b2c.PATH_FFT][1], ("single call", hs, ws, hk, wk))
+        p.destroy()
+
+
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
     """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
     rng = np.random.default_rng(14)
