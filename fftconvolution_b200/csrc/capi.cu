@@ -234,11 +234,11 @@ int auto_path(const Plan2D& pl, bool shared) {
                      pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
   // tuned kernels: 5.6 ps (P <= 80) or 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 1 ns
   const double pp = (double)pl.h.P * pl.w.P;
-  // tuned 1-D kernels (conv_tuned1d.cu): 6.3 ps per point of the period
+  // tuned 1-D kernels (conv_tuned1d.cu): 6.3 ps per point of the period (4.5 ps up to period 512)
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
                       pl.w.fold == 0 && pl.w.kwrap == pl.w.P;
   const double t_fft = tuned    ? (pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.0e-9
-                       : tuned1 ? 6.3e-12 * pl.w.P + 0.3e-9
+                       : tuned1 ? (pl.w.P <= 512 ? 4.5e-12 * pl.w.P : 6.3e-12 * pl.w.P + 0.3e-9)
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
   int spw;
