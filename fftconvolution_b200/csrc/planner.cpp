@@ -272,7 +272,8 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
   if (hs == 1 && hk == 1 && !out.w.exact && out.w.fold == 0) {
     for (int pm : kMenu1D) {
       if (pm < out.w.min_period) continue;
-      if (pm <= out.w.min_period + (out.w.min_period * 3) / 5) out.w.P = pm;
+      // (short signals: even twice the points beats the any-size kernel, which is overhead-bound there)
+      if (pm <= out.w.min_period + (out.w.min_period * 3) / 5 || (pm <= 512 && pm <= 2 * out.w.min_period)) out.w.P = pm;
       break;
     }
   }
