@@ -57,6 +57,8 @@ cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd,
                           double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
 // util_kernels.cu
 cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long first, cudaStream_t st);
+cudaError_t launch_balance(const double* d_src, long src_sz, const double* d_ker, long ker_sz, long ker_stride, long n,
+                           double* d_alpha, unsigned long long* d_maxima, int sms, cudaStream_t st);
 cudaError_t launch_checksum(const double* d, long n, unsigned long long* d_out3, cudaStream_t st);
 }  // namespace b2c
 
@@ -180,6 +182,8 @@ struct b2c_plan {
   cplx* kspec = nullptr;
   size_t kspec_bytes = 0;
   cplx* work = nullptr;
+  double* alpha = nullptr;     // per-image kernel scales of the packed-transform kernels (balance_kernel)
+  long alpha_n = 0;
   size_t work_slabs = 0;
   size_t work_slab_bytes = 0;
   // single-image host path staging: device [src | kernel | dst], pinned host [src | kernel]; the
@@ -285,6 +289,22 @@ int ensure_kspec(b2c_plan* p, size_t bytes) {
   return 0;
 }
 
+// Per-image power-of-two kernel scales for the kernels that transform source and kernel as one complex image.
+int compute_balance(b2c_plan* p, const double* d_src, const double* d_ker, int shared, long n, cudaStream_t st) {
+  if (p->alpha_n < n) {
+    if (p->alpha) CUDA_TRY(cudaFree(p->alpha));
+    p->alpha = nullptr; p->alpha_n = 0;
+    CUDA_TRY(cudaMalloc(&p->alpha, sizeof(double) * 3 * (size_t)n));   // [n] alpha, then [2 n] maxima scratch
+    p->alpha_n = n;
+  }
+  const Plan2D& pl = p->pl;
+  const long ssz = (long)pl.h.n_src * pl.w.n_src, ksz = (long)pl.h.n_ker * pl.w.n_ker;
+  CUDA_TRY(launch_balance(d_src, ssz, d_ker, ksz, shared ? 0 : ksz, n, p->alpha,
+                          reinterpret_cast<unsigned long long*>(p->alpha + p->alpha_n), p->ctx->sms, st));
+  g_launches += 2;
+  return 0;
+}
+
 // Shared-kernel plans whose periods are 108 x 108 run on the tuned kernel (conv_tuned108.cu).
 bool tuned108_applies(const b2c_plan* p, int shared) {
   const Plan2D& pl = p->pl;
@@ -379,6 +399,10 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
     p->work_slabs = slabs; p->work_slab_bytes = slab_per_cta;
   }
   q.slab = p->work;
+  if (!tuned) {   // conv_big2d.cu reads per-image scales; conv_big2ds.cu computes them itself
+    if (int rc = compute_balance(p, d_src, d_ker, shared, n, st)) return rc;
+    q.alpha = p->alpha;
+  }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_timer.on && g_timer.ev.size() < 8192) {
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
@@ -393,6 +417,7 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
       qg.src = d_src + (size_t)g0 * q.hs * q.ws;
       qg.ker = d_ker + (size_t)g0 * q.ker_stride;
       qg.dst = d_dst + (size_t)g0 * q.hd * q.wd;
+      qg.alpha = q.alpha + g0;
       int launches = 0;
       CUDA_TRY(launch_conv_big2d_split(qg, smem, st, &launches));
       g_launches += launches;
@@ -511,7 +536,7 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
     CUDA_TRY(cudaEventRecord(e0, st));
   }
   if (shared) CUDA_TRY(launch_conv_shared(q, grid, threads, wb, st));
-  else CUDA_TRY(launch_conv_perimage(q, grid, threads, wb, st));
+  else CUDA_TRY(launch_conv_perimage(q, grid, threads, std::max<size_t>(wb, 512), st));   // >= 64 doubles: cta_balance scratch
   ++g_launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
   return 0;
@@ -749,6 +774,7 @@ int b2c_plan_destroy(b2c_plan* p) {
   if (!p) return 0;
   if (p->kspec) cudaFree(p->kspec);
   if (p->work) cudaFree(p->work);
+  if (p->alpha) cudaFree(p->alpha);
   if (p->d_one) cudaFree(p->d_one);
   if (p->h_one) cudaFreeHost(p->h_one);
   free_pipe(p);

@@ -39,10 +39,12 @@ struct BigCtx {
   bool plain_kernel;
   float inv_ldw, inv_hw, inv_ldc, inv_wd, inv_pw;
   cplx *slabS, *slabK, *slabY;
+  double alpha;   // power-of-two scale of the kernel rows in the packed row transforms (balance_kernel)
 };
 
-__device__ __forceinline__ BigCtx big_ctx(const BigParams& p, size_t slab_index) {
+__device__ __forceinline__ BigCtx big_ctx(const BigParams& p, size_t slab_index, long img) {
   BigCtx c;
+  c.alpha = img < p.n_images ? __ldg(p.alpha + img) : 1.0;
   c.W = reinterpret_cast<cplx*>(b2c_smem_big);
   c.Ph = p.ah.P; c.Pw = p.aw.P;
   c.hke = min(p.hk, p.kwrap_h); c.wke = min(p.wk, p.kwrap_w);
@@ -72,7 +74,7 @@ __device__ __forceinline__ void big_phase_r(const BigParams& p, const BigCtx& x,
       v[q] = make_double2(0.0, 0.0);
       if (idx < nelem) {
         if (r < p.hs && c < p.ws) v[q].x = __ldg(&a[(size_t)r * p.ws + c]);
-        if (r < x.hke && c < x.wke) v[q].y = x.plain_kernel ? __ldg(&k[(size_t)r * p.wk + c]) : big_wrapped_tap(p, k, r, c);
+        if (r < x.hke && c < x.wke) v[q].y = x.alpha * (x.plain_kernel ? __ldg(&k[(size_t)r * p.wk + c]) : big_wrapped_tap(p, k, r, c));
       }
     }
 #pragma unroll
@@ -123,11 +125,12 @@ __device__ __forceinline__ void big_phase_c(const BigParams& p, const BigCtx& x,
   }
   __syncthreads();
   fft_forward(p.ah, W, p.ldc, 1, 2 * nc, true);
+  const double sc = p.scale / x.alpha;
   for (int idx = threadIdx.x; idx < Ph * nc; idx += blockDim.x) {   // convolution_fftw.h:195-204, 210-211
     const int r = idx / nc, c = idx - r * nc;
     const cplx s = W[r * p.ldc + c], kk = W[r * p.ldc + nc + c];
     const cplx y = cmul(s, kk);
-    W[r * p.ldc + c] = make_double2(y.x * p.scale, y.y * p.scale);
+    W[r * p.ldc + c] = make_double2(y.x * sc, y.y * sc);
   }
   __syncthreads();
   fft_backward(p.ah, W, p.ldc, 1, nc, true);
@@ -182,10 +185,11 @@ __device__ __forceinline__ void big_phase_rp(const BigParams& p, const BigCtx& x
 
 // Persistent form: one CTA per SM owns an image and walks the three phases through its own slab.
 __global__ void __launch_bounds__(512, 1) conv_big2d_kernel(const __grid_constant__ BigParams p) {
-  const BigCtx x = big_ctx(p, blockIdx.x);
+  BigCtx x = big_ctx(p, blockIdx.x, blockIdx.x);
   const size_t src_sz = (size_t)p.hs * p.ws, dst_sz = (size_t)p.hd * p.wd;
   const int pairs = (p.hd + 1) / 2;
   for (long img = blockIdx.x; img < p.n_images; img += gridDim.x) {
+    x.alpha = __ldg(p.alpha + img);
     const double* a = p.src + (size_t)img * src_sz;
     const double* k = p.ker + (size_t)img * p.ker_stride;
     for (int r0 = 0; r0 < x.rows_in; r0 += p.rows_chunk) big_phase_r(p, x, a, k, r0);
@@ -201,7 +205,7 @@ template <int PHASE>
 __global__ void __launch_bounds__(512, 1) conv_big2d_phase_kernel(const __grid_constant__ BigParams p, int units) {
   const long img = blockIdx.x / units;
   const int unit = blockIdx.x - (int)(img * units);
-  const BigCtx x = big_ctx(p, (size_t)img);
+  const BigCtx x = big_ctx(p, (size_t)img, img);
   if (PHASE == 0) {
     big_phase_r(p, x, p.src + (size_t)img * p.hs * p.ws, p.ker + (size_t)img * p.ker_stride, unit * p.rows_chunk);
   } else if (PHASE == 1) {

@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
   const int rows_total = max(p.hs + hke, p.rows_y);
   cplx* slab = p.slab + (size_t)blockIdx.x * (size_t)rows_total * HW;
   __shared__ unsigned long long bar_storage;
+  __shared__ double row_unscale[64];   // per row of a chunk: 0.5 / (power-of-two scale of its kernel row)
   unsigned long long* bar = &bar_storage;
   unsigned bar_phase = 0;
   if (threadIdx.x == 0) {
@@ -229,9 +230,21 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
           if (r < p.hs && c < p.ws) v[u].x = __ldcs(arow + c);          // streamed once: evict first, keep the slabs in L2
           if (r < hke && c < wke) v[u].y = plain_kernel ? __ldcs(krow + c) : wrapped_tap(p, k, r, c);
         }
+        // Source row and kernel row share one transform and are separated again right after it: the kernel
+        // row is scaled to the source row's magnitude by a power of two (fft_device.cuh: balance_from_maxima;
+        // the reference transforms them separately, convolution_fftw.h:190-191), undone at the split.
+        double ms = 0.0, mk = 0.0;
+#pragma unroll
+        for (int u = 0; u < NCH; ++u) { ms = fmax(ms, fabs(v[u].x)); mk = fmax(mk, fabs(v[u].y)); }
+        // row maxima by their exponent words (one warp-reduce instruction each); alpha = 2^(exponent difference)
+        const unsigned es = __reduce_max_sync(0xffffffffu, (unsigned)__double2hiint(ms)) >> 20;
+        const unsigned ek = __reduce_max_sync(0xffffffffu, (unsigned)__double2hiint(mk)) >> 20;
+        const bool usable = es > 0 && ek > 0 && es < 2047 && ek < 2047;   // zero / subnormal / inf / nan rows: no scaling
+        const double al = usable ? __hiloint2double((int)((1023u + es - ek) << 20), 0) : 1.0;
+        if (lane == 0) row_unscale[rr] = 0.5 / al;
 #pragma unroll
         for (int u = 0; u < NCH; ++u)
-          if (lane + 32 * u < P) wrow[lane + 32 * u] = v[u];
+          if (lane + 32 * u < P) wrow[lane + 32 * u] = make_double2(v[u].x, v[u].y * al);
       }
       __syncthreads();
       B2C_T(0);
@@ -241,13 +254,14 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
       for (int rr = warp; rr < nr; rr += nwarps) {
         const int r = r0 + rr;
         const cplx* wrow = W + rr * ldw;
+        const double hk2 = row_unscale[rr];     // 0.5 / alpha of this row
         for (int v = lane; v < HW; v += 32) {
           const cplx z1 = wrow[F::pos_of(v)];
           const cplx z2 = wrow[F::pos_of(v ? P - v : 0)];
           const int v0 = v & ~(CS - 1), nc = min(CS, HW - v0);
           cplx* blk = slab + (size_t)rows_total * v0 + (v - v0);
           if (r < p.hs) blk[r * nc] = make_double2(0.5 * (z1.x + z2.x), 0.5 * (z1.y - z2.y));
-          if (r < hke) blk[(p.hs + r) * nc] = make_double2(0.5 * (z1.y + z2.y), 0.5 * (z2.x - z1.x));
+          if (r < hke) blk[(p.hs + r) * nc] = make_double2(hk2 * (z1.y + z2.y), hk2 * (z2.x - z1.x));
         }
       }
       __threadfence();          // slab rows must be in L2 and ordered before the copy engine reads them

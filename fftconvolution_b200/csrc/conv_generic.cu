@@ -148,6 +148,12 @@ __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_cons
   for (long img = blockIdx.x; img < p.n_images; img += gridDim.x) {
     const double* a = p.src + (size_t)img * src_sz;
     const double* k = p.ker + (size_t)img * ker_sz;
+    if (threadIdx.x == 0 && img + gridDim.x < p.n_images) {   // next image of this CTA -> L2
+      l2_prefetch(p.src + (size_t)(img + gridDim.x) * src_sz, src_sz * sizeof(double));
+      l2_prefetch(p.ker + (size_t)(img + gridDim.x) * ker_sz, ker_sz * sizeof(double));
+    }
+    // kernel part scaled to the source's magnitude (fft_device.cuh: cta_balance), undone in q
+    const double al = cta_balance(a, (int)src_sz, k, (int)ker_sz, reinterpret_cast<double*>(W));
     for (int base = threadIdx.x; base < Ph * ld; base += 4 * blockDim.x) {
       cplx v[4];
 #pragma unroll
@@ -157,7 +163,7 @@ __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_cons
         v[kq] = make_double2(0.0, 0.0);
         if (idx < Ph * ld) {
           if (r < p.hs && c < p.ws) v[kq].x = __ldg(&a[r * p.ws + c]);
-          if (r < hke && c < wke) v[kq].y = plain_kernel ? __ldg(&k[r * p.wk + c]) : wrapped_tap(p, k, r, c);
+          if (r < hke && c < wke) v[kq].y = al * (plain_kernel ? __ldg(&k[r * p.wk + c]) : wrapped_tap(p, k, r, c));
         }
       }
 #pragma unroll
@@ -171,7 +177,7 @@ __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_cons
     fft_forward(p.ah, W, ld, 1, Pw, true);
     // Z = S + iK.  S(w) = (Z(w)+conj Z(-w))/2, K(w) = (Z(w)-conj Z(-w))/(2i)
     // => S*K = (Z(w)^2 - conj(Z(-w))^2) / (4i).  The (-w) partner sits at (neg_h[r], neg_w[c]).
-    const double q = 0.25 * p.scale;
+    const double q = 0.25 * p.scale / al;
     for (int idx = threadIdx.x; idx < Ph * Pw; idx += blockDim.x) {
       const int r = fast_div(idx, Pw, inv_pw), c = idx - r * Pw;
       const int pr = __ldg(&p.ah.neg[r]), pc = __ldg(&p.aw.neg[c]);

@@ -59,6 +59,7 @@ struct BigParams {
   double* dst;
   long n_images;
   cplx* slab;        // [gridDim.x][max(hs + hke, rows_y) * half_w]: Y replaces S|K strip by strip
+  const double* alpha;   // [n_images]: power-of-two kernel scale of the packed row transforms (balance_kernel)
 };
 
 }  // namespace b2c

@@ -29,6 +29,60 @@ __device__ __forceinline__ cplx mul_mi(cplx a) { return make_double2(a.y, -a.x);
 __device__ __forceinline__ cplx mul_pi(cplx a) { return make_double2(-a.y, a.x); }
 __device__ __forceinline__ cplx cswap(cplx a) { return make_double2(a.y, a.x); }
 
+// One thread asks the copy engine to bring `bytes` of global memory into L2 (no registers, no waiting): the
+// next image of a persistent CTA, so that its first pass meets L2 latency instead of HBM latency.
+__device__ __forceinline__ void l2_prefetch(const void* p, size_t bytes) {
+  const unsigned n = (unsigned)(bytes & ~(size_t)15);
+  if ((reinterpret_cast<size_t>(p) & 15) == 0 && n >= 16)   // bulk operations need 16-byte alignment
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(n) : "memory");
+}
+
+// ---- magnitude balance of packed transforms ------------------------------------------------------
+// Kernels that transform a source and a kernel as ONE complex image (z = s + i*k, then a Hermitian split)
+// extract the kernel's spectrum as a difference of source-sized numbers: relative accuracy degrades by
+// max|s| / max|k|.  The reference transforms the two separately (convolution_fftw.h:190-191).  Cure: pack
+// z = s + i*alpha*k with alpha the power of two that equalises the magnitudes (exact), undo it in the scale.
+__device__ __forceinline__ double balance_from_maxima(double ms, double mk) {
+  if (!(ms > 0.0) || !(mk > 0.0) || !isfinite(ms) || !isfinite(mk)) return 1.0;
+  return exp2((double)(ilogb(ms) - ilogb(mk)));
+}
+
+// The whole CTA scans one image and its kernel (the data is read again right after: L2 hits) and returns alpha
+// to every thread.  `scratch`: 64 doubles any thread of the CTA can write (the still unused work buffer).
+// Contains two __syncthreads().
+__device__ __forceinline__ double cta_balance(const double* __restrict__ a, int na, const double* __restrict__ k, int nk,
+                                              double* scratch) {
+  double ms = 0.0, mk = 0.0;
+  constexpr int U = 8;   // independent loads in flight per thread: the scan is latency-bound otherwise
+  const int step = blockDim.x;
+  for (int base = threadIdx.x; base < na; base += U * step) {
+    double v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = base + u * step < na ? __ldg(a + base + u * step) : 0.0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) ms = fmax(ms, fabs(v[u]));
+  }
+  for (int base = threadIdx.x; base < nk; base += U * step) {
+    double v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = base + u * step < nk ? __ldg(k + base + u * step) : 0.0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) mk = fmax(mk, fabs(v[u]));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ms = fmax(ms, __shfl_xor_sync(0xffffffffu, ms, o));
+    mk = fmax(mk, __shfl_xor_sync(0xffffffffu, mk, o));
+  }
+  const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  if ((threadIdx.x & 31) == 0) { scratch[w] = ms; scratch[32 + w] = mk; }
+  __syncthreads();
+  ms = 0.0; mk = 0.0;
+  for (int i = 0; i < nw; ++i) { ms = fmax(ms, scratch[i]); mk = fmax(mk, scratch[32 + i]); }
+  __syncthreads();   // scratch may be overwritten after this
+  return balance_from_maxima(ms, mk);
+}
+
 // ---- forward DFT butterflies, w = exp(-2*pi*i/R), in registers --------------------------------
 template <int R>
 struct Bfly;

@@ -2,6 +2,8 @@
 // order-independent verification checksum the multi-GPU partitioner reduces.
 #include <cuda_runtime.h>
 
+#include "fft_device.cuh"
+
 namespace b2c {
 
 __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
@@ -39,6 +41,59 @@ __global__ void checksum_kernel(const double* __restrict__ d, long n, unsigned l
     atomicXor(&out3[1], x);
     atomicAdd(reinterpret_cast<double*>(&out3[2]), fs);  // informational only: order dependent
   }
+}
+
+// Per-image magnitude balance for conv_big2d.cu (see fft_device.cuh: balance_from_maxima).  The images can be
+// large and few: `chunks` CTAs scan one image, maxima are combined with atomicMax on the bit patterns
+// (non-negative doubles order like unsigned integers), a second tiny kernel turns them into alpha.
+__global__ void __launch_bounds__(256) absmax_kernel(const double* __restrict__ src, long src_sz,
+                                                     const double* __restrict__ ker, long ker_sz, long ker_stride,
+                                                     unsigned long long* __restrict__ maxima) {
+  __shared__ double red[2][8];
+  const long img = blockIdx.y;
+  const double* a = src + img * src_sz;
+  const double* k = ker + img * ker_stride;
+  const long stride = (long)gridDim.x * blockDim.x, first = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  double ms = 0.0, mk = 0.0;
+  for (long i = first; i < src_sz; i += stride) ms = fmax(ms, fabs(__ldg(a + i)));
+  for (long i = first; i < ker_sz; i += stride) mk = fmax(mk, fabs(__ldg(k + i)));
+  for (int o = 16; o > 0; o >>= 1) {
+    ms = fmax(ms, __shfl_xor_sync(0xffffffffu, ms, o));
+    mk = fmax(mk, __shfl_xor_sync(0xffffffffu, mk, o));
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ms; red[1][threadIdx.x >> 5] = mk; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { ms = fmax(ms, red[0][w]); mk = fmax(mk, red[1][w]); }
+    if (!(ms == ms)) ms = 0.0;   // NaN input: no scaling (the result is NaN either way)
+    if (!(mk == mk)) mk = 0.0;
+    atomicMax(maxima + 2 * img, (unsigned long long)__double_as_longlong(ms));
+    atomicMax(maxima + 2 * img + 1, (unsigned long long)__double_as_longlong(mk));
+  }
+}
+
+__global__ void balance_finalize_kernel(const unsigned long long* __restrict__ maxima, long n, double* __restrict__ alpha) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    alpha[i] = balance_from_maxima(__longlong_as_double((long long)maxima[2 * i]), __longlong_as_double((long long)maxima[2 * i + 1]));
+}
+
+// d_alpha: n doubles; d_maxima: 2 n words of scratch
+cudaError_t launch_balance(const double* d_src, long src_sz, const double* d_ker, long ker_sz, long ker_stride, long n,
+                           double* d_alpha, unsigned long long* d_maxima, int sms, cudaStream_t st) {
+  cudaError_t e = cudaMemsetAsync(d_maxima, 0, sizeof(unsigned long long) * 2 * (size_t)n, st);
+  if (e != cudaSuccess) return e;
+  long chunks = (2L * sms + n - 1) / n;                       // about two waves of CTAs
+  const long most = (src_sz + 256 * 16 - 1) / (256 * 16);     // at least 16 elements per thread
+  if (chunks > most) chunks = most;
+  if (chunks < 1) chunks = 1;
+  for (long i0 = 0; i0 < n; i0 += 65535) {                    // gridDim.y limit
+    const long ni = n - i0 < 65535 ? n - i0 : 65535;
+    absmax_kernel<<<dim3((unsigned)chunks, (unsigned)ni), 256, 0, st>>>(d_src + i0 * src_sz, src_sz, d_ker + i0 * ker_stride, ker_sz,
+                                                                  ker_stride, d_maxima + 2 * i0);
+  }
+  balance_finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_maxima, n, d_alpha);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long first, cudaStream_t st) {

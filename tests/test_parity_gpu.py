@@ -337,6 +337,37 @@ def test_circular_same_on_tuned_menu_periods(b2c, oracle, torch_cuda):
         p.destroy()
 
 
+def test_packed_transform_kernels_keep_accuracy_when_magnitudes_differ(b2c, oracle, torch_cuda):
+    """Kernels that transform source and kernel as ONE complex image (per-image kernels; strip mode) extract the
+    kernel spectrum as a difference of source-sized numbers: with images ~1e3 and kernels ~1e-4 the relative error
+    was ~1e-9 until the kernel part got a power-of-two scale that equalises the magnitudes (balance_kernel).  The
+    reference transforms the two separately (convolution_fftw.h:190-191); the 1e-12 bound must hold for any scaling."""
+    torch = torch_cuda
+    rng = np.random.default_rng(97)
+    cases = [(2, 40, 44, 9, 7, 5, 0),          # per-image kernels, work buffer in shared memory
+             (7, 100, 100, 100, 100, 3, 0),    # period 200: split form of the strip kernel (3 images)
+             (7, 100, 100, 100, 100, 300, 0),  # ... persistent form (conv_big2ds.cu)
+             (0, 150, 130, 31, 60, 2, 1),      # strip mode, shared kernel, split form
+             (2, 170, 90, 40, 120, 160, 1)]    # strip mode, shared kernel, persistent form
+    for (mode, hs, ws, hk, wk, n, shared) in cases:
+        for (s_scale, k_scale) in [(1e3, 1e-4), (1e-5, 3e2)]:
+            src = s_scale * (0.5 + rng.random((n, hs, ws)))
+            ker = k_scale * (rng.random((hk, wk)) if shared else rng.random((n, hk, wk)))
+            if not shared:
+                ker[n - 1] *= 1e-3            # scales differ between images of one batch
+            p = b2c.Plan(mode, hs, ws, hk, wk)
+            p.set_path(b2c.PATH_FFT)
+            d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+            d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), shared, d_dst.data_ptr(), n, 0)
+            torch.cuda.synchronize()
+            got = d_dst.cpu().numpy()
+            for i in sorted({0, n - 1}):
+                _check(got[i], oracle.convolve_direct8(mode, src[i], ker if shared else ker[i]),
+                       ("magnitudes", mode, hs, ws, hk, wk, n, shared, s_scale, k_scale, i))
+            p.destroy()
+
+
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
     """BASELINE config 4 at sizes the oracle finishes in seconds: odd/even source x odd/even kernel."""
     rng = np.random.default_rng(14)
