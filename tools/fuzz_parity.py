@@ -24,7 +24,8 @@ for case in range(ncases):
         wk = int(rng.integers(1, min(600, 2 * ws + 2)))
         if rng.random() < 0.3: hs, ws, hk, wk = ws, hs, wk, hk
     else:
-        hs, ws = pick_dim(140), pick_dim(140)
+        big = 260 if rng.random() < 0.15 else 140
+        hs, ws = pick_dim(big), pick_dim(big)
         hk, wk = pick_dim(60), pick_dim(60)
     mode = int(rng.integers(0, 8))
     shared = int(rng.random() < 0.7)
@@ -37,7 +38,10 @@ for case in range(ncases):
         print("plan failed", mode, hs, ws, hk, wk, e); fails += 1; continue
     if p.h_dst == 0:
         p.destroy(); continue
-    src = rng.random((n, hs, ws)); ker = rng.random((hk, wk)) if shared else rng.random((n, hk, wk))
+    # magnitudes of source and kernel vary independently over twelve decades (one scale per batch: kernels that
+    # carry two images per transform bound the magnitude ratio of neighbours)
+    s_scale, k_scale = 10.0 ** rng.uniform(-6, 6), 10.0 ** rng.uniform(-6, 6)
+    src = s_scale * (rng.random((n, hs, ws)) - 0.3); ker = k_scale * ((rng.random((hk, wk)) if shared else rng.random((n, hk, wk))) - 0.3)
     want = [orc.convolve_direct8(mode, src[i], ker if shared else ker[i]) for i in sorted({0, n - 1})]
     d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
     for path in (b2c.PATH_AUTO, b2c.PATH_FFT, b2c.PATH_FFT_GENERIC, b2c.PATH_DIRECT):
