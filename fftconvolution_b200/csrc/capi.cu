@@ -535,7 +535,7 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
     CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
     CUDA_TRY(cudaEventRecord(e0, st));
   }
-  if (shared) CUDA_TRY(launch_conv_shared(q, grid, threads, wb, st));
+  if (shared) CUDA_TRY(launch_conv_shared(q, grid, threads, std::max<size_t>(wb, 512), st));
   else CUDA_TRY(launch_conv_perimage(q, grid, threads, std::max<size_t>(wb, 512), st));   // >= 64 doubles: cta_balance scratch
   ++g_launches;
   if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }

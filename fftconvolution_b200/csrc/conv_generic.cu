@@ -88,6 +88,10 @@ __global__ void __launch_bounds__(512, 1) conv_shared_kernel(const __grid_consta
     const double* a = p.src + (size_t)(2 * pair) * src_sz;
     const bool has_b = 2 * pair + 1 < p.n_images;
     const double* b = a + src_sz;
+    // two images ride one transform: image b is scaled by the power of two that equalises the pair's magnitudes
+    // (fft_device.cuh: cta_balance) so that the larger image's rounding noise does not land on the smaller one
+    const double beta = has_b ? cta_balance(a, (int)src_sz, b, (int)src_sz, reinterpret_cast<double*>(W)) : 1.0;
+    const double unbeta = 1.0 / beta;
     // zero-pad on load (convolution_fftw.h:174-183; the source never wraps because P >= n_src)
     // (four elements per thread per trip: eight independent global loads in flight before the stores)
     for (int base = threadIdx.x; base < Ph * ld; base += 4 * blockDim.x) {
@@ -99,7 +103,7 @@ __global__ void __launch_bounds__(512, 1) conv_shared_kernel(const __grid_consta
         v[k] = make_double2(0.0, 0.0);
         if (idx < Ph * ld && r < p.hs && c < p.ws) {
           v[k].x = __ldg(&a[r * p.ws + c]);
-          if (has_b) v[k].y = __ldg(&b[r * p.ws + c]);
+          if (has_b) v[k].y = beta * __ldg(&b[r * p.ws + c]);
         }
       }
 #pragma unroll
@@ -125,7 +129,7 @@ __global__ void __launch_bounds__(512, 1) conv_shared_kernel(const __grid_consta
       const int i = fast_div(idx, p.wd, inv_wd), j = idx - i * p.wd;
       cplx v = folded_value(p, W, i, j);
       da[idx] = v.x;
-      if (has_b) db[idx] = v.y;
+      if (has_b) db[idx] = v.y * unbeta;
     }
     __syncthreads();
   }

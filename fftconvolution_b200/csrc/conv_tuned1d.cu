@@ -54,6 +54,7 @@ struct Geo {
   static constexpr int SLOTS = P + P / LAST;
   static constexpr size_t smem_bytes = sizeof(cplx) * (size_t)SLOTS;
   static __host__ __device__ constexpr int pad(int p) { return p + p / LAST; }
+  static constexpr bool ONE_ROUND = P / R0 <= THREADS;   // first pass: one butterfly per thread
   static constexpr int MIN_CTAS = 2 * smem_bytes <= 225 * 1024 ? 2 : 1;   // register budget follows the CTAs that fit
   // Twiddle tables, one per pass that has twiddles: entry (q-1) * M + j = w_N^(j*q).  Reading tw[j*q*TSTEP]
   // instead costs one 32-byte sector per lane (ncu: L1TEX 83 % busy, long-scoreboard the top stall).
@@ -70,7 +71,7 @@ struct Geo {
 //   MULK       : M == 1: forward butterfly, multiply by the kernel spectrum, backward butterfly
 template <class G, int P, int N, int R, bool INV, bool SRC_GLOBAL, bool DST_GLOBAL, bool MULK, int TOFF>
 __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, const double* b2, double* da, double* db,
-                                     cplx wj = make_double2(1.0, 0.0)) {
+                                     cplx wj = make_double2(1.0, 0.0), double bs = 1.0) {   // bs: factor on signal b (see first_pass_pair)
   constexpr int M = N / R;
   // first / last pass with one butterfly per thread: the thread's j never changes, its root w_P^j lives in
   // registers and the R-1 twiddles are its powers (17 dependent multiplications cost less than 17 table
@@ -90,7 +91,7 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
           int si = pos - p.shift;
           if (si < 0) si += p.ns;
           v[q].x = __ldg(a + si);
-          if (b2) v[q].y = __ldg(b2 + si);
+          if (b2) v[q].y = bs * __ldg(b2 + si);
         }
       }
       if (p.n_in > P) {   // samples congruent modulo the period add up (a kernel longer than the period,
@@ -151,7 +152,7 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
         const int d = base + M * q - p.off;
         if (d >= 0 && d < p.nd) {
           da[d] = v[q].x;
-          if (db) db[d] = v[q].y;
+          if (db) db[d] = v[q].y * bs;
         }
       }
     } else {
@@ -161,10 +162,68 @@ __device__ __forceinline__ void pass(cplx* W, const Params& p, const double* a, 
   }
 }
 
+// First forward pass of a PAIR of signals with one butterfly per thread.  Two signals ride one complex
+// transform; the rounding noise of the larger one would land on the smaller one, so signal b is scaled by the
+// power of two `beta` that equalises the two maxima (exact; undone when the result is stored) -- the reference
+// transforms every signal on its own (convolution_fftw.h:190).  All threads of the CTA must call this
+// (one __syncthreads inside); returns beta.
+template <class G, int P, int R>
+__device__ __forceinline__ double first_pass_pair(cplx* W, const Params& p, const double* a, const double* b2, cplx wj,
+                                                  unsigned* red) {
+  constexpr int M = P / R;
+  static_assert(M <= G::THREADS, "one butterfly per thread");
+  const bool active = threadIdx.x < M;
+  const int j = active ? threadIdx.x : 0;
+  cplx v[R];
+#pragma unroll
+  for (int q = 0; q < R; ++q) {
+    const int pos = j + M * q;
+    v[q] = make_double2(0.0, 0.0);
+    if (active && pos < p.n_in) {
+      int si = pos - p.shift;
+      if (si < 0) si += p.ns;
+      v[q].x = __ldg(a + si);
+      v[q].y = __ldg(b2 + si);
+    }
+  }
+  double ma = 0.0, mb = 0.0;
+#pragma unroll
+  for (int q = 0; q < R; ++q) { ma = fmax(ma, fabs(v[q].x)); mb = fmax(mb, fabs(v[q].y)); }
+  const unsigned wa = __reduce_max_sync(0xffffffffu, (unsigned)__double2hiint(ma)) >> 20;   // exponent words
+  const unsigned wb = __reduce_max_sync(0xffffffffu, (unsigned)__double2hiint(mb)) >> 20;
+  const int warp = threadIdx.x >> 5;
+  constexpr int NW = G::THREADS / 32;
+  if ((threadIdx.x & 31) == 0) { red[warp] = wa; red[NW + warp] = wb; }
+  __syncthreads();
+  unsigned ea = 0, eb = 0;
+#pragma unroll
+  for (int w = 0; w < NW; ++w) { ea = max(ea, red[w]); eb = max(eb, red[NW + w]); }
+  const bool usable = ea > 0 && eb > 0 && ea < 2047 && eb < 2047;   // zero / subnormal / inf / nan: no scaling
+  const double beta = usable ? __hiloint2double((int)((1023u + ea - eb) << 20), 0) : 1.0;
+  if (active) {
+#pragma unroll
+    for (int q = 0; q < R; ++q) v[q].y *= beta;
+    BigBfly<R>::run(v);
+    constexpr bool POW = B2C_T1_POW && R <= 16;
+    if (POW) {
+      cplx cur = wj;
+#pragma unroll
+      for (int q = 1; q < R; ++q) { v[q] = cmul(v[q], cur); cur = cmul(cur, wj); }
+    } else {
+#pragma unroll
+      for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(p.twtab + G::OFF0 + (q - 1) * M + j));
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q) W[G::pad(j + M * q)] = v[q];
+  }
+  return beta;
+}
+
 template <int P, int R0, int R1, int R2, int R3>
-__device__ __forceinline__ void forward_all_but_last(cplx* W, const Params& p, const double* a, const double* b2, cplx wj) {
+__device__ __forceinline__ void forward_all_but_last(cplx* W, const Params& p, const double* a, const double* b2, cplx wj,
+                                                     bool first_done = false, double bs = 1.0) {
   typedef Geo<P, R0, R1, R2, R3> G;
-  pass<G, P, P, R0, false, true, false, false, G::OFF0>(W, p, a, b2, nullptr, nullptr, wj);
+  if (!first_done) pass<G, P, P, R0, false, true, false, false, G::OFF0>(W, p, a, b2, nullptr, nullptr, wj, bs);
   __syncthreads();
   if (G::NS == 4) {
     pass<G, P, P / R0, R1, false, false, false, false, G::OFF1>(W, p, nullptr, nullptr, nullptr, nullptr);
@@ -181,6 +240,7 @@ template <int P, int R0, int R1, int R2, int R3>
 __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0, R1, R2, R3>::MIN_CTAS)) conv_kernel(const __grid_constant__ Params p) {
   typedef Geo<P, R0, R1, R2, R3> G;
   cplx* W = reinterpret_cast<cplx*>(b2c_smem_t1);
+  __shared__ unsigned red[2 * (G::THREADS / 32)];
   const long pairs = (p.n_signals + 1) / 2;
   const cplx wj = __ldg(p.tw + (threadIdx.x < P / R0 ? threadIdx.x : 0));   // w_P^j of this thread's first-pass butterfly
   for (long pr = blockIdx.x; pr < pairs; pr += gridDim.x) {
@@ -189,7 +249,18 @@ __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0,
     const double* b2 = two ? a + p.ns : nullptr;
     double* da = p.dst + (size_t)(2 * pr) * p.nd;
     double* db = two ? da + p.nd : nullptr;
-    forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2, wj);
+    double beta = 1.0;   // power-of-two factor on signal b that equalises the pair's magnitudes
+    if (two) {
+      if constexpr (G::ONE_ROUND) {
+        beta = first_pass_pair<G, P, R0>(W, p, a, b2, wj, red);
+        forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2, wj, true);
+      } else {
+        beta = cta_balance(a, p.ns, b2, p.ns, reinterpret_cast<double*>(W));
+        forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2, wj, false, beta);
+      }
+    } else {
+      forward_all_but_last<P, R0, R1, R2, R3>(W, p, a, b2, wj);
+    }
     pass<G, P, G::LAST, G::LAST, false, false, false, true, -1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
     if (G::NS == 4) {
@@ -198,7 +269,7 @@ __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0,
     }
     pass<G, P, P / R0, R1, true, false, false, false, G::OFF1>(W, p, nullptr, nullptr, nullptr, nullptr);
     __syncthreads();
-    pass<G, P, P, R0, true, false, true, false, G::OFF0>(W, p, nullptr, nullptr, da, db, wj);
+    pass<G, P, P, R0, true, false, true, false, G::OFF0>(W, p, nullptr, nullptr, da, db, wj, 1.0 / beta);
     __syncthreads();   // the next pair's first pass overwrites W
   }
 }

@@ -366,6 +366,24 @@ def test_packed_transform_kernels_keep_accuracy_when_magnitudes_differ(b2c, orac
                 _check(got[i], oracle.convolve_direct8(mode, src[i], ker if shared else ker[i]),
                        ("magnitudes", mode, hs, ws, hk, wk, n, shared, s_scale, k_scale, i))
             p.destroy()
+    # two signals per transform (1-D family): neighbours of a batch that differ by 1e9 in magnitude
+    for (ns, nk) in [(1000, 255), (4096, 63), (100, 40), (4096, 4096), (1000, -255), (77, -30)]:   # negative: any-size kernel
+        generic = nk < 0
+        nk = abs(nk)
+        n = 6
+        src = rng.random((n, 1, ns)) - 0.5
+        src[1] *= 1e9; src[2] *= 1e-7; src[5] *= 1e5
+        ker = rng.random((1, nk))
+        p = b2c.Plan(b2c.LINEAR_SAME, 1, ns, 1, nk)
+        p.set_path(b2c.PATH_FFT_GENERIC if generic else b2c.PATH_FFT)
+        d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+        d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+        p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), n, 0)
+        torch.cuda.synchronize()
+        got = d_dst.cpu().numpy()
+        for i in range(n):
+            _check(got[i], oracle.convolve_direct8(b2c.LINEAR_SAME, src[i], ker), ("pair magnitudes", ns, nk, i, generic))
+        p.destroy()
 
 
 def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
