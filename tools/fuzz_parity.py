@@ -38,10 +38,10 @@ for case in range(ncases):
         print("plan failed", mode, hs, ws, hk, wk, e); fails += 1; continue
     if p.h_dst == 0:
         p.destroy(); continue
-    # magnitudes of source and kernel vary independently over twelve decades (one scale per batch: kernels that
-    # carry two images per transform bound the magnitude ratio of neighbours)
+    # magnitudes of source and kernel vary independently over twelve decades, images of a batch over eight
     s_scale, k_scale = 10.0 ** rng.uniform(-6, 6), 10.0 ** rng.uniform(-6, 6)
-    src = s_scale * (rng.random((n, hs, ws)) - 0.3); ker = k_scale * ((rng.random((hk, wk)) if shared else rng.random((n, hk, wk))) - 0.3)
+    src = s_scale * (rng.random((n, hs, ws)) - 0.3) * (10.0 ** rng.uniform(-4, 4, size=(n, 1, 1)));   # neighbours differ too
+    ker = k_scale * ((rng.random((hk, wk)) if shared else rng.random((n, hk, wk))) - 0.3)
     want = [orc.convolve_direct8(mode, src[i], ker if shared else ker[i]) for i in sorted({0, n - 1})]
     d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
     for path in (b2c.PATH_AUTO, b2c.PATH_FFT, b2c.PATH_FFT_GENERIC, b2c.PATH_DIRECT):
