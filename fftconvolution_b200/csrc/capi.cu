@@ -42,13 +42,6 @@ size_t tuned1d_scratch_elems(int P);
 cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, int n_in, int shift, const double* d_src, const double* d_ker,
                            double* d_dst, long n, cplx* scratch, int build_table, const cplx* tw, int sms,
                            cudaStream_t st, int* launches);
-// conv_tuned108.cu
-size_t tuned108_smem_bytes();
-size_t tuned108_kspec_bytes();
-int tuned108_occupancy();
-cudaError_t launch_tuned108_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st);
-cudaError_t launch_tuned108_conv(int hs, int ws, int hd, int wd, int off_h, int off_w, const double* d_src,
-                                 double* d_dst, long n, const cplx* kspec, const cplx* tw, int grid, cudaStream_t st);
 // conv_tuned2.cu
 bool tuned2_has(int P);
 size_t tuned2_kspec_bytes(int P);
@@ -305,35 +298,6 @@ int compute_balance(b2c_plan* p, const double* d_src, const double* d_ker, int s
   return 0;
 }
 
-// Shared-kernel plans whose periods are 108 x 108 run on the tuned kernel (conv_tuned108.cu).
-bool tuned108_applies(const b2c_plan* p, int shared) {
-  const Plan2D& pl = p->pl;
-  return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == 108 && pl.w.P == 108 &&
-         pl.h.fold == 0 && pl.w.fold == 0 && pl.h.kwrap == 108 && pl.w.kwrap == 108;
-}
-
-int run_tuned108(b2c_plan* p, const double* d_src, const double* d_ker, double* d_dst, long n, cudaStream_t st) {
-  const Plan2D& pl = p->pl;
-  if (int rc = ensure_kspec(p, work_bytes(pl))) return rc;
-  if (!p->kspec_reuse) {
-    CUDA_TRY(launch_tuned108_kspec(d_ker, pl.h.n_ker, pl.w.n_ker, p->tw.tw, p->kspec, st));
-    ++g_launches;
-  }
-  const int occ = tuned108_occupancy();
-  if (occ < 1) return fail(B2C_ECUDA, "tuned 108x108 kernel cannot be resident");
-  int grid = (int)std::min<long>(n, (long)p->ctx->sms * occ);
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (g_timer.on && g_timer.ev.size() < 8192) {
-    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
-    CUDA_TRY(cudaEventRecord(e0, st));
-  }
-  CUDA_TRY(launch_tuned108_conv(pl.h.n_src, pl.w.n_src, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off, d_src, d_dst,
-                                n, p->kspec, p->tw.tw, grid, st));
-  ++g_launches;
-  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
-  return 0;
-}
-
 // Plans whose full complex work buffer exceeds shared memory run in strip mode (conv_big2d.cu):
 // row chunks / column strips in shared memory, half spectra through an L2-resident slab.
 int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst, long n,
@@ -490,7 +454,6 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
   // 14.5 M for the older hand-written conv_tuned108.cu, bit-identical results; that file now only serves the
   // static-scratch entry point, whose scratch layout it defines)
   if (tuned2_applies(p, p->pl, shared)) return run_tuned2(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
-  if (tuned108_applies(p, shared)) return run_tuned108(p, d_src, d_ker, d_dst, n, st);
   if (tuned1d_applies(p, p->pl, shared)) return run_tuned1d(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&
       p->forced_path != B2C_PATH_FFT_GENERIC)
