@@ -137,17 +137,44 @@ int get_tables(DeviceCtx* c, const AxisPlan& a, AxisTables* out) {
   CUDA_TRY(cudaMemcpy(t.tw, tw.data(), sizeof(cplx) * P, cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(t.neg, neg.data(), sizeof(int) * P, cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(t.posf, pos_of.data(), sizeof(int) * P, cudaMemcpyHostToDevice));
+  // A copy from pageable memory may return while its DMA is still in flight, and the kernels that read these
+  // tables run on the caller's (possibly non-blocking) stream: wait for the tables once, here.
+  CUDA_TRY(cudaStreamSynchronize(0));
   c->tables[P] = t;
   *out = t;
   return 0;
 }
 
+// Event pairs around the dominant kernel of each compute call (b2c_kernel_timer).  Every launch path may run on
+// one host thread per device (b2c_multi_convolve_batch_host), so the list is guarded.
 struct KernelTimer {
-  bool on = false;
+  std::mutex mu;
+  std::atomic<bool> on{false};
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
   void clear() {
+    std::lock_guard<std::mutex> lk(mu);
     for (auto& e : ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     ev.clear();
+  }
+  // records the start event on `st`; *e0 stays null when the timer is off or full
+  cudaError_t begin(cudaStream_t st, cudaEvent_t* e0, cudaEvent_t* e1) {
+    *e0 = *e1 = nullptr;
+    if (!on.load()) return cudaSuccess;
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      if (ev.size() >= 8192) return cudaSuccess;
+    }
+    cudaError_t e = cudaEventCreate(e0);
+    if (e == cudaSuccess) e = cudaEventCreate(e1);
+    if (e == cudaSuccess) e = cudaEventRecord(*e0, st);
+    return e;
+  }
+  cudaError_t end(cudaStream_t st, cudaEvent_t e0, cudaEvent_t e1) {
+    if (!e0) return cudaSuccess;
+    cudaError_t e = cudaEventRecord(e1, st);
+    std::lock_guard<std::mutex> lk(mu);
+    ev.emplace_back(e0, e1);
+    return e;
   }
 };
 KernelTimer g_timer;
@@ -368,10 +395,7 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
     q.alpha = p->alpha;
   }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (g_timer.on && g_timer.ev.size() < 8192) {
-    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
-    CUDA_TRY(cudaEventRecord(e0, st));
-  }
+  CUDA_TRY(g_timer.begin(st, &e0, &e1));
   // A batch that cannot occupy half the machine with one CTA per image runs one launch per phase,
   // every chunk / strip of every image on its own CTA (conv_big2d.cu, split form).
   if (split) {
@@ -391,7 +415,7 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
     else CUDA_TRY(launch_conv_big2d(q, grid, smem, st));
     ++g_launches;
   }
-  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  CUDA_TRY(g_timer.end(st, e0, e1));
   return 0;
 }
 
@@ -405,16 +429,13 @@ int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const doubl
                cudaStream_t st) {
   if (int rc = ensure_kspec(p, std::max(work_bytes(pl), tuned2_kspec_bytes(pl.h.P)))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (g_timer.on && g_timer.ev.size() < 8192) {
-    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
-    CUDA_TRY(cudaEventRecord(e0, st));
-  }
+  CUDA_TRY(g_timer.begin(st, &e0, &e1));
   int launches = 0;
   CUDA_TRY(launch_tuned2(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
                          pl.w.off, pl.h.n_in, pl.w.n_in, pl.h.src_shift, pl.w.src_shift, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n,
                          p->kspec, tww.tw, p->ctx->sms, st, &launches));
   g_launches += launches;
-  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  CUDA_TRY(g_timer.end(st, e0, e1));
   return 0;
 }
 
@@ -429,16 +450,13 @@ int run_tuned1d(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const doub
                 cudaStream_t st) {
   if (int rc = ensure_kspec(p, std::max(work_bytes(pl), sizeof(cplx) * tuned1d_scratch_elems(pl.w.P)))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (g_timer.on && g_timer.ev.size() < 8192) {
-    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
-    CUDA_TRY(cudaEventRecord(e0, st));
-  }
+  CUDA_TRY(g_timer.begin(st, &e0, &e1));
   int launches = 0;
   CUDA_TRY(launch_tuned1d(pl.w.P, pl.w.n_src, pl.w.n_ker, pl.w.n_dst, pl.w.off, pl.w.n_in, pl.w.src_shift, d_src,
                           p->kspec_reuse ? nullptr : d_ker, d_dst, n, p->kspec, p->t1d_tables ? 0 : 1, tww.tw, p->ctx->sms, st, &launches));
   p->t1d_tables = true;
   g_launches += launches;
-  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  CUDA_TRY(g_timer.end(st, e0, e1));
   return 0;
 }
 
@@ -497,14 +515,11 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
       ++g_launches;
     }
   }
-  if (g_timer.on && g_timer.ev.size() < 8192) {
-    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
-    CUDA_TRY(cudaEventRecord(e0, st));
-  }
+  CUDA_TRY(g_timer.begin(st, &e0, &e1));
   if (shared) CUDA_TRY(launch_conv_shared(q, grid, threads, std::max<size_t>(wb, 512), st));
   else CUDA_TRY(launch_conv_perimage(q, grid, threads, std::max<size_t>(wb, 512), st));   // >= 64 doubles: cta_balance scratch
   ++g_launches;
-  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  CUDA_TRY(g_timer.end(st, e0, e1));
   return 0;
 }
 
@@ -548,13 +563,10 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);
   if (grid < 1) grid = 1;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (g_timer.on && g_timer.ev.size() < 8192) {
-    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
-    CUDA_TRY(cudaEventRecord(e0, st));
-  }
+  CUDA_TRY(g_timer.begin(st, &e0, &e1));
   CUDA_TRY(launch_direct(q, grid, smem, st));
   ++g_launches;
-  if (e0) { CUDA_TRY(cudaEventRecord(e1, st)); g_timer.ev.emplace_back(e0, e1); }
+  CUDA_TRY(g_timer.end(st, e0, e1));
   return 0;
 }
 
@@ -911,13 +923,14 @@ int b2c_host_free(void* p) {
 
 int b2c_kernel_timer(int enable) {
   g_timer.clear();
-  g_timer.on = enable != 0;
+  g_timer.on.store(enable != 0);
   return 0;
 }
 
 int b2c_kernel_timer_read(double* avg_ms, long* launches) {
   double total = 0;
   long n = 0;
+  std::lock_guard<std::mutex> lk(g_timer.mu);
   for (auto& e : g_timer.ev) {
     CUDA_TRY(cudaEventSynchronize(e.second));
     float ms = 0;

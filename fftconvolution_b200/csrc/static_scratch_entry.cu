@@ -91,6 +91,10 @@ int set_up_device(int dev, PerDevice** out) {
     }
     e = cudaMemcpy(d.base + kRootsOffset, roots, kRootsBytes, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return cuda_fail("cudaMemcpy(root table)", e);
+    // the copy comes from pageable memory and may return before its DMA has landed; the kernels below run on
+    // the caller's stream, which need not be ordered after the legacy stream: wait here, once per device
+    e = cudaStreamSynchronize(0);
+    if (e != cudaSuccess) return cuda_fail("cudaStreamSynchronize(root table)", e);
     e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return cuda_fail("cudaDeviceGetAttribute", e);
     d.ctas_per_sm = b2c::tuned108_occupancy();
