@@ -48,6 +48,11 @@ size_t tuned2_kspec_bytes(int P);
 cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
                           int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker,
                           double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
+// conv_pfa108.cu
+size_t pfa108_kspec_bytes();
+cudaError_t launch_pfa108(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int hs_in, int ws_in,
+                          int sh_h, int sh_w, const double* d_src, const double* d_ker, double* d_dst, long n,
+                          cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
 // util_kernels.cu
 cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long first, cudaStream_t st);
 cudaError_t launch_balance(const double* d_src, long src_sz, const double* d_ker, long ker_sz, long ker_stride, long n,
@@ -427,10 +432,19 @@ bool tuned2_applies(const b2c_plan* p, const Plan2D& pl, int shared) {
 
 int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const double* d_src, const double* d_ker, double* d_dst, long n,
                cudaStream_t st) {
-  if (int rc = ensure_kspec(p, std::max(work_bytes(pl), tuned2_kspec_bytes(pl.h.P)))) return rc;
+  // period 108 (the headline shape): the five-pass prime-factor kernel of conv_pfa108.cu; B2C_P108=t2 keeps the
+  // (12, 9) member of the seven-pass family for A/B measurements
+  static const bool p108_t2 = [] { const char* e = getenv("B2C_P108"); return e && !strcmp(e, "t2"); }();
+  const bool pfa = pl.h.P == 108 && !p108_t2;
+  if (int rc = ensure_kspec(p, std::max(work_bytes(pl), std::max(tuned2_kspec_bytes(pl.h.P), pfa108_kspec_bytes())))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   CUDA_TRY(g_timer.begin(st, &e0, &e1));
   int launches = 0;
+  if (pfa)
+    CUDA_TRY(launch_pfa108(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
+                           pl.h.n_in, pl.w.n_in, pl.h.src_shift, pl.w.src_shift, d_src, p->kspec_reuse ? nullptr : d_ker,
+                           d_dst, n, p->kspec, tww.tw, p->ctx->sms, st, &launches));
+  else
   CUDA_TRY(launch_tuned2(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
                          pl.w.off, pl.h.n_in, pl.w.n_in, pl.h.src_shift, pl.w.src_shift, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n,
                          p->kspec, tww.tw, p->ctx->sms, st, &launches));

@@ -14,20 +14,24 @@ namespace b2c {
 
 typedef double2 cplx;
 
-__device__ __forceinline__ cplx cadd(cplx a, cplx b) { return make_double2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ cplx csub(cplx a, cplx b) { return make_double2(a.x - b.x, a.y - b.y); }
-__device__ __forceinline__ cplx cmul(cplx a, cplx b) {
+// complex arithmetic and register butterflies are plain math: also compilable for the host (tools/emulate_pfa108.cu
+// steps the headline kernel's passes thread by thread on the CPU as a development aid -- never a product path)
+#define B2C_MATH __host__ __device__ __forceinline__
+
+B2C_MATH cplx cadd(cplx a, cplx b) { return make_double2(a.x + b.x, a.y + b.y); }
+B2C_MATH cplx csub(cplx a, cplx b) { return make_double2(a.x - b.x, a.y - b.y); }
+B2C_MATH cplx cmul(cplx a, cplx b) {
   return make_double2(fma(a.x, b.x, -a.y * b.y), fma(a.x, b.y, a.y * b.x));
 }
 // a * conj(b)
-__device__ __forceinline__ cplx cmulc(cplx a, cplx b) {
+B2C_MATH cplx cmulc(cplx a, cplx b) {
   return make_double2(fma(a.x, b.x, a.y * b.y), fma(a.y, b.x, -a.x * b.y));
 }
 // -i * a
-__device__ __forceinline__ cplx mul_mi(cplx a) { return make_double2(a.y, -a.x); }
+B2C_MATH cplx mul_mi(cplx a) { return make_double2(a.y, -a.x); }
 // +i * a
-__device__ __forceinline__ cplx mul_pi(cplx a) { return make_double2(-a.y, a.x); }
-__device__ __forceinline__ cplx cswap(cplx a) { return make_double2(a.y, a.x); }
+B2C_MATH cplx mul_pi(cplx a) { return make_double2(-a.y, a.x); }
+B2C_MATH cplx cswap(cplx a) { return make_double2(a.y, a.x); }
 
 // One thread asks the copy engine to bring `bytes` of global memory into L2 (no registers, no waiting): the
 // next image of a persistent CTA, so that its first pass meets L2 latency instead of HBM latency.
@@ -89,7 +93,7 @@ struct Bfly;
 
 template <>
 struct Bfly<2> {
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     cplx a = v[0], b = v[1];
     v[0] = cadd(a, b);
     v[1] = csub(a, b);
@@ -98,7 +102,7 @@ struct Bfly<2> {
 
 template <>
 struct Bfly<3> {
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     const double s = 0.86602540378443864676;  // sin(2*pi/3)
     cplx t = cadd(v[1], v[2]);
     cplx d = csub(v[1], v[2]);
@@ -112,7 +116,7 @@ struct Bfly<3> {
 
 template <>
 struct Bfly<4> {
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     cplx a = cadd(v[0], v[2]), b = csub(v[0], v[2]);
     cplx c = cadd(v[1], v[3]), d = mul_mi(csub(v[1], v[3]));
     v[0] = cadd(a, c);
@@ -124,7 +128,7 @@ struct Bfly<4> {
 
 template <>
 struct Bfly<5> {
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     const double c1 = 0.30901699437494742410;   // cos(2*pi/5)
     const double c2 = -0.80901699437494742410;  // cos(4*pi/5)
     const double s1 = 0.95105651629515357212;   // sin(2*pi/5)
@@ -146,7 +150,7 @@ struct Bfly<5> {
 
 template <>
 struct Bfly<7> {
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     const double c1 = 0.62348980185873353053;   // cos(2*pi/7)
     const double c2 = -0.22252093395631440429;  // cos(4*pi/7)
     const double c3 = -0.90096886790241912624;  // cos(6*pi/7)
@@ -182,7 +186,7 @@ struct Bfly<7> {
 
 template <>
 struct Bfly<8> {
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     const double h = 0.70710678118654752440;  // 1/sqrt(2)
     cplx e[4] = {v[0], v[2], v[4], v[6]};
     cplx o[4] = {v[1], v[3], v[5], v[7]};
@@ -202,7 +206,7 @@ struct Bfly<8> {
 // Forward DFT of R points in registers for every radix the tuned kernels use: the plain butterflies above,
 // prime-factor compositions of them (6, 10, 12, 14, 18, 20) and Cooley-Tukey 3x3 / 4x4 (9, 16).
 template <int R>
-struct BigBfly { static __device__ __forceinline__ void run(cplx* v) { Bfly<R>::run(v); } };
+struct BigBfly { static B2C_MATH void run(cplx* v) { Bfly<R>::run(v); } };
 
 // ---- small-radix butterflies by prime-factor (Good-Thomas) composition: no internal twiddles ----
 __host__ __device__ constexpr int inv_mod(int a, int m) {
@@ -213,7 +217,7 @@ __host__ __device__ constexpr int inv_mod(int a, int m) {
 
 // N = A * B, gcd(A, B) = 1: input n = (B*n1 + A*n2) mod N, output k = (B*B'*k1 + A*A'*k2) mod N
 template <int A, int B>
-__device__ __forceinline__ void bfly_pfa(cplx* v) {
+B2C_MATH void bfly_pfa(cplx* v) {
   constexpr int N = A * B;
   constexpr int ea = B * inv_mod(B % A, A), eb = A * inv_mod(A % B, B);
   cplx u[A][B];
@@ -237,12 +241,12 @@ __device__ __forceinline__ void bfly_pfa(cplx* v) {
   }
 }
 
-template <> struct BigBfly<6> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 3>(v); } };
-template <> struct BigBfly<10> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 5>(v); } };
-template <> struct BigBfly<12> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<3, 4>(v); } };
-template <> struct BigBfly<14> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 7>(v); } };
+template <> struct BigBfly<6> { static B2C_MATH void run(cplx* v) { bfly_pfa<2, 3>(v); } };
+template <> struct BigBfly<10> { static B2C_MATH void run(cplx* v) { bfly_pfa<2, 5>(v); } };
+template <> struct BigBfly<12> { static B2C_MATH void run(cplx* v) { bfly_pfa<3, 4>(v); } };
+template <> struct BigBfly<14> { static B2C_MATH void run(cplx* v) { bfly_pfa<2, 7>(v); } };
 template <> struct BigBfly<9> {
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     const cplx w1 = make_double2(0.76604444311897803520, -0.64278760968653932632);
     const cplx w2 = make_double2(0.17364817766693034885, -0.98480775301220805937);
     const cplx w4 = make_double2(-0.93969262078590838405, -0.34202014332566873304);
@@ -261,7 +265,7 @@ template <> struct BigBfly<9> {
   }
 };
 template <> struct BigBfly<16> {   // 4 x 4 Cooley-Tukey, twiddles w16^(n1*k2)
-  static __device__ __forceinline__ void run(cplx* v) {
+  static B2C_MATH void run(cplx* v) {
     const double c1 = 0.92387953251128675613, s1 = 0.38268343236508977173, h = 0.70710678118654752440;
     cplx a[4][4];   // a[n1][k2]: DFT4 over n2 of v[n1 + 4*n2]
 #pragma unroll
@@ -287,8 +291,8 @@ template <> struct BigBfly<16> {   // 4 x 4 Cooley-Tukey, twiddles w16^(n1*k2)
   }
 };
 
-template <> struct BigBfly<18> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<2, 9>(v); } };
-template <> struct BigBfly<20> { static __device__ __forceinline__ void run(cplx* v) { bfly_pfa<4, 5>(v); } };
+template <> struct BigBfly<18> { static B2C_MATH void run(cplx* v) { bfly_pfa<2, 9>(v); } };
+template <> struct BigBfly<20> { static B2C_MATH void run(cplx* v) { bfly_pfa<4, 5>(v); } };
 
 // One radix-R stage over `nlines` independent lines living in one work buffer.
 //   element k of line l is at  W[l*ls + k*es]
