@@ -227,6 +227,142 @@ def allreduce_u64_sum(torch, dist, world, word):
     return (lo + (hi << 32)) & 0xFFFFFFFFFFFFFFFF
 
 
+# ---- secondary workloads (BASELINE.json configs 3, 4, 1 and a strong-scaling split of config 2) ------------
+SEED3, SEED4 = 0x5EED0003, 0x5EED0004
+N3 = 16384          # config 3: images per GPU
+N4 = 16384          # config 4: signals per GPU
+
+
+class Ctx:
+    """What the timed regions share: torch handles, rank layout, the launching stream."""
+
+    def __init__(self, torch, dist, b2c, rank, world, local_rank):
+        self.torch, self.dist, self.b2c = torch, dist, b2c
+        self.rank, self.world, self.local_rank = rank, world, local_rank
+        self.stream = torch.cuda.current_stream().cuda_stream
+        self.peak, self.peak_kind = measured_peak()
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x):
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(self, fn, steps, warmup=3):
+        """ms per step of fn() on the launching stream (CUDA events, barrier + synchronize on both sides, max
+        over ranks) and the clocks sampled during that region."""
+        torch = self.torch
+        for _ in range(warmup):
+            fn()
+        self.barrier()
+        sampler = ClockSampler(self.local_rank)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.start()
+        self.barrier()
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        sampler.sample()
+        self.barrier()
+        sampler.sample()
+        sampler.stop_flag = True
+        return self.max_over_ranks(ev0.elapsed_time(ev1)) / steps, sampler.result()
+
+
+def device_batch_record(cx, name, mode, hs, ws, hk, wk, n, shared, seed, steps, bytes_per_conv):
+    """One secondary record: `n` problems per GPU, inputs generated on the device, kernel(s) included in the step."""
+    torch, b2c = cx.torch, cx.b2c
+    plan = b2c.Plan(mode, hs, ws, hk, wk)
+    first, _ = b2c.partition(n * cx.world, cx.world, cx.rank)
+    d_src = torch.empty((n, hs, ws), dtype=torch.float64, device="cuda")
+    d_ker = torch.empty((1 if shared else n, hk, wk), dtype=torch.float64, device="cuda")
+    d_dst = torch.empty((n, plan.h_dst, plan.w_dst), dtype=torch.float64, device="cuda")
+    b2c.fill_uniform_device(d_src.data_ptr(), d_src.numel(), seed, first * hs * ws, cx.stream)
+    b2c.fill_uniform_device(d_ker.data_ptr(), d_ker.numel(), seed ^ 0xABCDEF0000, 0 if shared else first * hk * wk, cx.stream)
+
+    def step():
+        plan.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1 if shared else 0, d_dst.data_ptr(), n, cx.stream)
+
+    ms, clocks = cx.timed(step, steps)
+    cs = allreduce_u64_sum(torch, cx.dist, cx.world, b2c.checksum_device(d_dst.data_ptr(), d_dst.numel(), cx.stream)[0])
+    value = n * cx.world / (ms * 1e-3)
+    gbs = n * bytes_per_conv / (ms * 1e-3) / 1e9
+    rec = {"name": name, "value": value, "unit": UNIT, "ms_per_step": ms, "steps": steps, "per_gpu": n,
+           "fft_period": [plan.h_fft, plan.w_fft], "path": plan.info()["path"],
+           "roofline": {"bound": "hbm", "achieved": gbs, "peak": cx.peak, "unit": "GB/s", "frac": gbs / cx.peak,
+                        "algorithmic_bytes_per_conv": bytes_per_conv, "peak_kind": cx.peak_kind},
+           "clocks": clocks, "checksum_u64": cs}
+    plan.destroy()
+    del d_src, d_ker, d_dst
+    torch.cuda.empty_cache()
+    return rec
+
+
+def single_call_record(cx):
+    """configs[0]: one 50x50 (*) 10x10 LINEAR_SAME convolution per call through b2c_convolve_host, which is what
+    the drop-in header's convolve(ws, src, kernel) calls (pageable src/kernel, page-locked ws.dst): H2D, kernel,
+    D2H and the synchronisation are all inside the timed call.  Inputs as convolution_benchmark.cc:137-145."""
+    import numpy as np
+    b2c = cx.b2c
+    L = b2c.lib()
+    rng = np.random.default_rng(1)
+    src, ker = rng.random((50, 50)), rng.random((10, 10))
+    plan = b2c.Plan(b2c.LINEAR_SAME, 50, 50, 10, 10)
+    pinned = ctypes.c_void_p()
+    b2c.capi.check(L.b2c_host_alloc(ctypes.byref(pinned), 50 * 50 * 8))
+    for _ in range(20):
+        b2c.capi.check(L.b2c_convolve_host(plan._h, src.ctypes.data, ker.ctypes.data, pinned))
+    cx.barrier()
+    sampler = ClockSampler(cx.local_rank)
+    sampler.start()
+    calls = 300
+    t0 = time.perf_counter()
+    for _ in range(calls):
+        L.b2c_convolve_host(plan._h, src.ctypes.data, ker.ctypes.data, pinned)
+    dt = time.perf_counter() - t0
+    sampler.sample()
+    sampler.stop_flag = True
+    dt = cx.max_over_ranks(dt)
+    got = np.ctypeslib.as_array(ctypes.cast(pinned, ctypes.POINTER(ctypes.c_double)), shape=(50, 50)).copy()
+    L.b2c_host_free(pinned)
+    plan.destroy()
+    return {"name": "configs[0]: single 50x50 (*) 10x10 LINEAR_SAME per convolve() call, host buffers", "value": calls / dt,
+            "unit": "conv/s", "us_per_call": 1e6 * dt / calls, "calls": calls, "result_norm": float(np.linalg.norm(got)),
+            "clocks": sampler.result()}
+
+
+def pcie_probe(cx, mb=512):
+    """Raw ceiling of the end-to-end leg: one page-locked H2D copy and one D2H copy of `mb` MiB running
+    concurrently on two streams, all ranks at once; GB/s each way per GPU (the slower direction)."""
+    torch = cx.torch
+    n = mb << 20
+    h_in = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(n, dtype=torch.uint8).pin_memory()
+    d_in = torch.empty(n, dtype=torch.uint8, device="cuda")
+    d_out = torch.empty(n, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    best = None
+    for it in range(3):
+        cx.barrier()
+        t0 = time.perf_counter()
+        with torch.cuda.stream(s1):
+            d_in.copy_(h_in, non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.synchronize()
+        dt = cx.max_over_ranks(time.perf_counter() - t0)
+        if it:
+            best = dt if best is None else min(best, dt)
+    del h_in, h_out, d_in, d_out
+    return n / best / 1e9
+
+
 def run_b2c_arm(args):
     import numpy as np
     import torch
@@ -330,13 +466,72 @@ def run_b2c_arm(args):
     except Exception as ex:  # pinned allocation can fail on a small host; say so instead of faking a number
         e2e = {"value": None, "unit": UNIT, "error": str(ex)[:200]}
 
+    cx = Ctx(torch, dist, b2c, rank, world, local_rank)
+    if e2e and e2e.get("value"):
+        try:   # name the ceiling of the end-to-end leg: raw concurrent page-locked copies on this box
+            gbs = pcie_probe(cx)
+            e2e["pcie_gbs_each_way_per_gpu"] = gbs
+            e2e["roof"] = world * gbs * 1e9 / (H * W * 8)
+            e2e["frac"] = e2e["value"] / e2e["roof"]
+        except Exception as ex:
+            e2e["pcie_probe_error"] = str(ex)[:120]
+
+    # ---- strong scaling: the SAME 65536 images split over the ranks (b2c_partition); the all-reduced checksum of
+    # the shards must equal the checksum of rank 0's own full batch from the weak run above (images [0, 65536))
+    strong = None
+    try:
+        ref_cs = torch.tensor([cs[0] & 0xFFFFFFFF, (cs[0] >> 32) & 0xFFFFFFFF], dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.broadcast(ref_cs, src=0)
+        ref_word = (int(ref_cs[0].item()) + (int(ref_cs[1].item()) << 32)) & 0xFFFFFFFFFFFFFFFF
+        g_begin, g_end = b2c.partition(args.batch, world, rank)
+        m = g_end - g_begin
+        if world > 1:
+            b2c.fill_uniform_device(d_src.data_ptr(), m * H * W, SEED, g_begin * H * W, stream)
+
+        def strong_step():
+            plan.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 1, d_dst.data_ptr(), m, stream)
+
+        s_ms, s_clocks = cx.timed(strong_step, args.steps)
+        s_cs = allreduce_u64_sum(torch, dist, world, b2c.checksum_device(d_dst.data_ptr(), m * H * W, stream)[0])
+        strong = {"name": "configs[1] split over the ranks: 65536 images in total", "value": args.batch / (s_ms * 1e-3),
+                  "unit": UNIT, "ms_per_step": s_ms, "steps": args.steps, "images_total": args.batch, "scaling": "strong",
+                  "checksum_u64": s_cs, "checksum_n1": ref_word, "checksum_matches_n1": bool(s_cs == ref_word),
+                  "clocks": s_clocks}
+    except Exception as ex:
+        strong = {"error": str(ex)[:200]}
+
+    secondary = []
+    if not args.no_secondary:
+        del d_src, d_dst
+        torch.cuda.empty_cache()
+        jobs = [
+            ("configs[2]: 100x100 (*) 100x100 CIRCULAR_FULL, per-image kernels, %d per GPU" % N3,
+             b2c.CIRCULAR_FULL, 100, 100, 100, 100, N3, False, SEED3, 5, 8 * (2 * 100 * 100 + 199 * 199)),
+            ("configs[3]: 1x4096 (*) 1x255 LINEAR_SAME rows, shared kernel, %d per GPU" % N4,
+             b2c.LINEAR_SAME, 1, 4096, 1, 255, N4, True, SEED4, 20, 8 * (4096 + 4096)),
+            ("configs[3]: 4096x1 (*) 255x1 LINEAR_SAME columns, shared kernel, %d per GPU" % N4,
+             b2c.LINEAR_SAME, 4096, 1, 255, 1, N4, True, SEED4, 20, 8 * (4096 + 4096)),
+            ("configs[3]: 1x4095 (*) 1x256 LINEAR_FULL rows (odd source, even kernel), shared kernel, %d per GPU" % N4,
+             b2c.LINEAR_FULL, 1, 4095, 1, 256, N4, True, SEED4, 20, 8 * (4095 + 4350)),
+        ]
+        for job in jobs:
+            try:
+                secondary.append(device_batch_record(cx, *job))
+            except Exception as ex:
+                secondary.append({"name": job[0], "error": str(ex)[:200]})
+        try:
+            secondary.append(single_call_record(cx))
+        except Exception as ex:
+            secondary.append({"name": "configs[0]", "error": str(ex)[:200]})
+
     peak, peak_kind = measured_peak()
     kernel_s = avg_ms.value * 1e-3
     achieved = (n_local * ALGO_BYTES_PER_CONV / kernel_s) / 1e9 if kernel_s > 0 else None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(),
                 "peak_kind": peak_kind,
-                "kernel": "b2c::t2::conv_kernel<12,9>" if (plan.h_fft, plan.w_fft) == (108, 108) else "b2c::conv_shared_kernel", "kernel_ms": avg_ms.value,
+                "kernel": ("b2c::t2::conv_kernel<12,9>" if os.environ.get("B2C_P108") == "t2" else "b2c::pfa::conv_kernel") if (plan.h_fft, plan.w_fft) == (108, 108) else "b2c::conv_shared_kernel", "kernel_ms": avg_ms.value,
                 "kernel_launches": nl.value, "algorithmic_bytes_per_launch": n_local * ALGO_BYTES_PER_CONV}
 
     cpu_baseline = None
@@ -387,6 +582,7 @@ def run_b2c_arm(args):
                        "rng": "splitmix64 seed 0x5EED0002 on device"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": sampler.result(), "checksum_u64": checksum,
+            "strong": strong, "secondary": secondary,
         }
         emit_line(line)
     if world > 1:
@@ -422,6 +618,7 @@ def main():
     ap.add_argument("--e2e-batch", type=int, default=BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    ap.add_argument("--no-secondary", action="store_true", help="profiling runs: skip the secondary workloads")
     args = ap.parse_args()
     claim_stdout()
     if args.impl == "reference":

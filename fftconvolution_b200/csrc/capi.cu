@@ -424,6 +424,15 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
   return 0;
 }
 
+// Strip mode needs one full row and a strip of one column pair in shared memory.  A long 1-D transform that is
+// neither on the tuned 1-D menu nor small enough for this (e.g. 1 x 20000 (*) 1 x 20000 LINEAR_FULL) runs on the
+// any-size kernel with its work buffer in global memory instead.
+bool big2d_fits(const b2c_plan* p) {
+  const size_t smem_max = (size_t)p->ctx->smem_optin;
+  const int ldw = p->pl.w.P | 1;
+  return (int)(smem_max / (sizeof(cplx) * ldw)) >= 1 && ((int)(smem_max / (sizeof(cplx) * p->pl.h.P)) - 1) / 2 >= 1;
+}
+
 // Shared-kernel plans with equal periods from the tuned menu (conv_tuned2.cu).
 bool tuned2_applies(const b2c_plan* p, const Plan2D& pl, int shared) {
   return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == pl.w.P && tuned2_has(pl.h.P) &&
@@ -488,7 +497,7 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
   if (tuned2_applies(p, p->pl, shared)) return run_tuned2(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (tuned1d_applies(p, p->pl, shared)) return run_tuned1d(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&
-      p->forced_path != B2C_PATH_FFT_GENERIC)
+      p->forced_path != B2C_PATH_FFT_GENERIC && (p->strip_only || big2d_fits(p)))
     return run_big2d(p, d_src, d_ker, shared, d_dst, n, st);
   ConvParams q;
   memset(&q, 0, sizeof q);

@@ -401,6 +401,31 @@ def test_one_d_up_to_4096(b2c, oracle, torch_cuda):
             p.destroy()
 
 
+def test_one_d_per_image_kernels_and_beyond_the_menu(b2c, oracle, torch_cuda):
+    """1-D rows and columns with PER-SIGNAL kernels (batch), and a 1 x 20000 (*) 1 x 20000 LINEAR_FULL plan whose period is
+    beyond both the tuned 1-D menu and strip mode: it runs on the any-size kernel with its work buffer in global memory."""
+    torch = torch_cuda
+    rng = np.random.default_rng(16)
+    n = 5
+    for mode, ns, nk in [(0, 257, 30), (2, 1000, 255), (3, 4096, 100), (4, 777, 64), (7, 4095, 256), (5, 64, 63)]:
+        for column in (False, True):
+            shape_s, shape_k = ((ns, 1), (nk, 1)) if column else ((1, ns), (1, nk))
+            src, ker = rng.random((n,) + shape_s), rng.random((n,) + shape_k)
+            p = b2c.Plan(mode, *shape_s, *shape_k)
+            d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+            d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 0, d_dst.data_ptr(), n, 0)
+            torch.cuda.synchronize()
+            got = d_dst.cpu().numpy()
+            for i in (0, n - 1):
+                _check(got[i], oracle.convolve_direct8(mode, src[i], ker[i]), ("1-D per-signal kernels", mode, ns, nk, column, i))
+            p.destroy()
+    src, ker = rng.random((1, 20000)), rng.random((1, 20000))
+    p = b2c.Plan(b2c.LINEAR_FULL, 1, 20000, 1, 20000)
+    _check(p.convolve_host(src, ker), oracle.convolve_direct8(b2c.LINEAR_FULL, src, ker), "1 x 20000 (*) 1 x 20000")
+    p.destroy()
+
+
 def test_host_batch_pipeline_matches_device_batch(b2c, oracle, torch_cuda):
     rng = np.random.default_rng(15)
     n, hs, ws, hk, wk = 1500, 100, 100, 15, 15   # > one pipeline chunk

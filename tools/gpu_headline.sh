@@ -12,7 +12,7 @@ cat $O/ab.txt
 [ $rc -eq 0 ] || { echo "tests failed: no profiling"; exit 1; }
 python tools/trace_pfa108.py > $O/trace_pfa108.csv 2>&1; cat $O/trace_pfa108.csv
 python bench.py --steps 20 --warmup 3 > $O/bench.json 2> $O/bench.err; cat $O/bench.json
-CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
+CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-secondary"
 $CMD > $O/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $O/launches.csv $CMD > $O/ncu_launch.log 2>&1
 $CMD > $O/plain2.log 2>&1 &&
