@@ -441,10 +441,12 @@ bool tuned2_applies(const b2c_plan* p, const Plan2D& pl, int shared) {
 
 int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const double* d_src, const double* d_ker, double* d_dst, long n,
                cudaStream_t st) {
-  // period 108 (the headline shape): the five-pass prime-factor kernel of conv_pfa108.cu; B2C_P108=t2 keeps the
-  // (12, 9) member of the seven-pass family for A/B measurements
-  static const bool p108_t2 = [] { const char* e = getenv("B2C_P108"); return e && !strcmp(e, "t2"); }();
-  const bool pfa = pl.h.P == 108 && !p108_t2;
+  // period 108 (the headline shape) runs the (12, 9) member of the seven-pass family.  B2C_P108=pfa selects the
+  // five-pass prime-factor kernel of conv_pfa108.cu instead: a third less shared-memory traffic and no twiddle
+  // registers, but its 27-point transforms hold 108 of the 128 registers and it measured 15.1 against 15.7 M conv/s
+  // (profiles/r02_pfa108_*).  Kept for A/B measurements and under the parity tests.
+  const char* p108 = pl.h.P == 108 ? getenv("B2C_P108") : nullptr;   // read per call: the parity tests switch it
+  const bool pfa = p108 && !strcmp(p108, "pfa");
   if (int rc = ensure_kspec(p, std::max(work_bytes(pl), std::max(tuned2_kspec_bytes(pl.h.P), pfa108_kspec_bytes())))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   CUDA_TRY(g_timer.begin(st, &e0, &e1));
@@ -491,9 +493,6 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
     if (tuned2_applies(p, p->ext, shared)) return run_tuned2(p, p->ext, p->tw_ext, d_src, d_ker, d_dst, n, st);
     if (tuned1d_applies(p, p->ext, shared)) return run_tuned1d(p, p->ext, p->tw_ext, d_src, d_ker, d_dst, n, st);
   }
-  // (period 108: the template family's (12, 9) member measured 15.7 M conv/s on the headline workload against
-  // 14.5 M for the older hand-written conv_tuned108.cu, bit-identical results; that file now only serves the
-  // static-scratch entry point, whose scratch layout it defines)
   if (tuned2_applies(p, p->pl, shared)) return run_tuned2(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (tuned1d_applies(p, p->pl, shared)) return run_tuned1d(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&

@@ -42,49 +42,88 @@ struct Params {
   const cplx* kspec;   // [4 k4'][27 k27'][56 kk], pre-scaled by 0.5 / 108^2
 };
 
-constexpr int P = 108, HALF = 54, LD = 113, NU = 14, KK = 56, REGB = 56, THREADS = 256;
+constexpr int P = 108, HALF = 54, LD = 113, NU = 14, KK = 56, REGB = 56, THREADS = 224, LPAD = 56;
 constexpr size_t SMEM_BYTES = sizeof(cplx) * (size_t)HALF * LD;   // 97 632: two CTAs per SM inside the 196 KB carve-out
 
+// Constants of the 27-point DFT: sin(2 pi / 3), then exp(-2 pi i m / 27) for m = 1..8, 10, 12, 14, 16.  On the device
+// they are constant-bank operands of the FP64 instructions (literals would cost two uniform moves each and the
+// kernel must stay small: beyond ~40 KB of code the warps of two CTAs starve on instruction fetch).
+#define B2C_PFA_CONSTANTS                                                                                          \
+  0.8660254037844386467637, 0.9730448705798238388329, -0.2306158707424401784502, 0.8936326403234122481926,         \
+  -0.448799180200462172785, 0.7660444431189780352024, -0.6427876096865393263226, 0.5971585917027861648519,         \
+  -0.8021231927550437850833, 0.396079766039156823696, -0.918216106880274014759, 0.1736481776669303488517,          \
+  -0.9848077530122080593667, -0.05814482891047582853875, -0.9983081582712682080478, -0.2868032327110902531033,     \
+  -0.9579895123154888744374, -0.6862416378687335857296, -0.7273736415730486959872, -0.9396926207859083840541,      \
+  -0.3420201433256687330441, -0.9932383577419429885479, 0.1160929141252302296757, -0.8354878114129364196538,       \
+  0.5495089780708060352628
+__constant__ double c_pfa[25] = {B2C_PFA_CONSTANTS};
+static const double h_pfa[25] = {B2C_PFA_CONSTANTS};   // host copy, for the CPU emulation of the passes only
 #ifdef __CUDA_ARCH__
+#define B2C_PFA_K(i) c_pfa[i]
 #define B2C_PFA_LDG(ptr) __ldg(ptr)
 #else
+#define B2C_PFA_K(i) h_pfa[i]
 #define B2C_PFA_LDG(ptr) (*(ptr))
 #endif
-
-// exp(-2 pi i m / 27) for the exponents the 3 x 9 decomposition needs
-__host__ __device__ constexpr double w27_re(int m) {
-  return m == 1 ? 0.9730448705798238388329 : m == 2 ? 0.8936326403234122481926 : m == 3 ? 0.7660444431189780352024
-       : m == 4 ? 0.5971585917027861648519 : m == 5 ? 0.396079766039156823696 : m == 6 ? 0.1736481776669303488517
-       : m == 7 ? -0.05814482891047582853875 : m == 8 ? -0.2868032327110902531033 : m == 10 ? -0.6862416378687335857296
-       : m == 12 ? -0.9396926207859083840541 : m == 14 ? -0.9932383577419429885479 : m == 16 ? -0.8354878114129364196538 : 1.0;
+// Predicated global accesses: one instruction each, no branch and no select (a conditional expression compiles to a
+// branch per element here, and the passes must stay small and cheap to issue).
+B2C_MATH double ldg_if(const double* ptr, bool on) {
+#ifdef __CUDA_ARCH__
+  double v;
+  asm volatile("{\n .reg .pred p;\n setp.ne.u32 p, %2, 0;\n mov.f64 %0, 0d0000000000000000;\n @p ld.global.nc.f64 %0, [%1];\n}"
+               : "=d"(v) : "l"(ptr), "r"((unsigned)on));
+  return v;
+#else
+  return on ? *ptr : 0.0;
+#endif
 }
-__host__ __device__ constexpr double w27_im(int m) {
-  return m == 1 ? -0.2306158707424401784502 : m == 2 ? -0.448799180200462172785 : m == 3 ? -0.6427876096865393263226
-       : m == 4 ? -0.8021231927550437850833 : m == 5 ? -0.918216106880274014759 : m == 6 ? -0.9848077530122080593667
-       : m == 7 ? -0.9983081582712682080478 : m == 8 ? -0.9579895123154888744374 : m == 10 ? -0.7273736415730486959872
-       : m == 12 ? -0.3420201433256687330441 : m == 14 ? 0.1160929141252302296757 : m == 16 ? 0.5495089780708060352628 : 0.0;
+B2C_MATH void stg_if(double* ptr, double v, bool on) {
+#ifdef __CUDA_ARCH__
+  asm volatile("{\n .reg .pred p;\n setp.ne.u32 p, %2, 0;\n @p st.global.f64 [%0], %1;\n}" ::"l"(ptr), "d"(v), "r"((unsigned)on) : "memory");
+#else
+  if (on) *ptr = v;
+#endif
 }
 
-// Forward 27-point DFT in registers, natural order in and out: 27 = 3 x 9 Cooley-Tukey,
-// n = 9 a + b, k = ka + 3 kb:  DFT3 over a, twiddle W27^(b ka), DFT9 over b.  436 FP64 instructions.
+// table slot of exp(-2 pi i m / 27): m = 1..8 -> 1, 3, .., 15; 10, 12, 14, 16 -> 17, 19, 21, 23
+__host__ __device__ constexpr int w27_slot(int m) { return m <= 8 ? 2 * m - 1 : m + 7; }
+#define B2C_PFA_W27(m) make_double2(B2C_PFA_K(w27_slot(m)), B2C_PFA_K(w27_slot(m) + 1))
+
+B2C_MATH void dft3(cplx& a, cplx& b, cplx& c) {
+  const double s = B2C_PFA_K(0);
+  const cplx t = cadd(b, c), d = csub(b, c);
+  const cplx m = make_double2(fma(-0.5, t.x, a.x), fma(-0.5, t.y, a.y));
+  a = cadd(a, t);
+  b = make_double2(fma(s, d.y, m.x), fma(-s, d.x, m.y));
+  c = make_double2(fma(-s, d.y, m.x), fma(s, d.x, m.y));
+}
+
+// Forward 27-point DFT in registers, natural order in and out: 27 = 3 x 3 x 3 Cooley-Tukey with the constants
+// above; n = 9 a + b, k = ka + 3 kb: DFT3 over a, twiddle W27^(b ka), then a 9-point DFT over b (itself 3 x 3 with
+// W9 = W27^3).  436 FP64 instructions.
 B2C_MATH void dft27(cplx* v) {
 #pragma unroll
   for (int b = 0; b < 9; ++b) {
-    cplx t[3] = {v[b], v[b + 9], v[b + 18]};
-    Bfly<3>::run(t);
-    v[b] = t[0];
-    v[b + 9] = b ? cmul(t[1], make_double2(w27_re(b), w27_im(b))) : t[1];
-    v[b + 18] = b ? cmul(t[2], make_double2(w27_re(2 * b), w27_im(2 * b))) : t[2];
+    dft3(v[b], v[b + 9], v[b + 18]);
+    if (b) {
+      v[b + 9] = cmul(v[b + 9], B2C_PFA_W27(b));
+      v[b + 18] = cmul(v[b + 18], B2C_PFA_W27(2 * b));
+    }
   }
   cplx o[27];
 #pragma unroll
   for (int ka = 0; ka < 3; ++ka) {
-    cplx s[9];
+    cplx* x = v + 9 * ka;   // 9-point DFT of x[0..8] -> o[ka + 3 kb]
 #pragma unroll
-    for (int b = 0; b < 9; ++b) s[b] = v[9 * ka + b];
-    BigBfly<9>::run(s);
+    for (int c = 0; c < 3; ++c) dft3(x[c], x[c + 3], x[c + 6]);
+    x[4] = cmul(x[4], B2C_PFA_W27(3));  x[5] = cmul(x[5], B2C_PFA_W27(6));
+    x[7] = cmul(x[7], B2C_PFA_W27(6));  x[8] = cmul(x[8], B2C_PFA_W27(12));
 #pragma unroll
-    for (int kb = 0; kb < 9; ++kb) o[ka + 3 * kb] = s[kb];
+    for (int k1 = 0; k1 < 3; ++k1) {
+      dft3(x[3 * k1], x[3 * k1 + 1], x[3 * k1 + 2]);
+#pragma unroll
+      for (int k2 = 0; k2 < 3; ++k2) o[ka + 3 * (k1 + 3 * k2)] = x[3 * k1 + k2];
+    }
   }
 #pragma unroll
   for (int k = 0; k < 27; ++k) v[k] = o[k];
@@ -93,79 +132,90 @@ B2C_MATH void dft27(cplx* v) {
 // position of vertical (group g = k27, 4-point index s) inside a line
 __host__ __device__ constexpr int vpos(int g, int s) { return g < NU ? NU * s + g : REGB + NU * s + (27 - g); }
 
-// Rows of thread J = n4 in ascending order: row RHO + 4 m is element n27 = (m - O) mod 27 of its 27-point
-// sequence ((27 J + 4 n27) mod 108).  J is a template parameter (and warp-uniform at run time), so every row
-// number, register index and -- for stores into Z -- offset below is a compile-time constant.
-template <int J>
-struct Rows {
-  static constexpr int RHO = (27 * J) & 3, O = (27 * J - RHO) / 4;
-  static __host__ __device__ constexpr int n_of(int m) { return (m - O + 27) % 27; }
+// ---- pass 1: vertical 27-point DFTs, global -> Z.  Thread (n4 = j = t / 56, line = t % 56 < 54): element n27 of
+// its sequence is row (27 j + 4 n27) mod 108, columns `line` (real part) and `line + 54` (imaginary part).
+struct VThread {   // what a thread of passes 1 and 5 keeps across images
+  int j, line;
+  bool act;
 };
+// The row numbers of a thread depend only on its n4: left alone, the compiler hoists all 27 of them (and the offsets
+// and predicates built on them) out of the image loop and pins ~60 registers for the whole kernel, which starves
+// every other pass.  Re-deriving them per image costs a few integer instructions; this hides the invariance.
+B2C_MATH int opaque(int x) {
+#ifdef __CUDA_ARCH__
+  asm volatile("" : "+r"(x));
+#endif
+  return x;
+}
+B2C_MATH VThread vthread(int t) {
+  VThread q;
+  q.j = t / LPAD; q.line = t - q.j * LPAD;
+  q.act = q.line < HALF;
+  return q;
+}
 
-template <int J>
-B2C_MATH void load_rows(cplx* v, const Params& p, const double* __restrict__ x, int line) {
-  typedef Rows<J> R;
-  const bool c0 = line < p.ws_in, c1 = line + HALF < p.ws_in;
-  if ((p.sh_h | p.sh_w) == 0) {
-    // rows RHO + 4 m < hs  <=>  m < mv; the column tests are folded into the two row limits
-    const int mv = (p.hs - R::RHO + 3) >> 2;
-    const int mv0 = c0 ? mv : 0, mv1 = c1 ? mv : 0;
-    const unsigned ws = (unsigned)p.ws, base = (unsigned)line + R::RHO * ws;
+// EXT: the periodic-extension form of CIRCULAR_SAME (its own kernel instantiation: the common form stays small)
+template <bool EXT>
+B2C_MATH void p1_load(cplx* v, const VThread& q, const Params& p, const double* __restrict__ x) {
+  const bool c0 = q.line < p.ws_in, c1 = q.line + HALF < p.ws_in;
+  const int j27 = opaque(27 * q.j);
+  if (!EXT) {
+    const int h0 = c0 ? p.hs : 0, h1 = c1 ? p.hs : 0;   // column tests folded into the row limits
+    const unsigned ws = (unsigned)p.ws;
+    const double* xc = x + q.line;
 #pragma unroll
-    for (int m = 0; m < 27; ++m) {
-      const unsigned off = base + (4u * m) * ws;
-      v[R::n_of(m)].x = m < mv0 ? B2C_PFA_LDG(x + off) : 0.0;
-      v[R::n_of(m)].y = m < mv1 ? B2C_PFA_LDG(x + off + HALF) : 0.0;
+    for (int n = 0; n < 27; ++n) {
+      int r = j27 + 4 * n;
+      if (r >= P) r -= P;
+      const double* xr = xc + (unsigned)r * ws;
+      v[n].x = ldg_if(xr, r < h0);
+      v[n].y = ldg_if(xr + HALF, r < h1);
     }
   } else {   // source extended periodically by (sh_h, sh_w) samples in front
-    int sc0 = line - p.sh_w, sc1 = line + HALF - p.sh_w;
+    int sc0 = q.line - p.sh_w, sc1 = q.line + HALF - p.sh_w;
     if (sc0 < 0) sc0 += p.ws;
     if (sc1 < 0) sc1 += p.ws;
 #pragma unroll
-    for (int m = 0; m < 27; ++m) {
-      const int r = R::RHO + 4 * m;
+    for (int n = 0; n < 27; ++n) {
+      int r = j27 + 4 * n;
+      if (r >= P) r -= P;
       int sr = r - p.sh_h;
       if (sr < 0) sr += p.hs;
       const bool in = r < p.hs_in;
-      v[R::n_of(m)].x = (in && c0) ? B2C_PFA_LDG(x + (unsigned)(sr * p.ws + sc0)) : 0.0;
-      v[R::n_of(m)].y = (in && c1) ? B2C_PFA_LDG(x + (unsigned)(sr * p.ws + sc1)) : 0.0;
+      v[n].x = (in && c0) ? B2C_PFA_LDG(x + (unsigned)(sr * p.ws + sc0)) : 0.0;
+      v[n].y = (in && c1) ? B2C_PFA_LDG(x + (unsigned)(sr * p.ws + sc1)) : 0.0;
     }
   }
 }
-
-template <int J>
-B2C_MATH void store_rows(const cplx* v, const Params& p, double* __restrict__ y, int line) {
-  typedef Rows<J> R;
-  const int j0 = line - p.off_w, j1 = line + HALF - p.off_w;
-  // output row i = RHO + 4 m - off_h must lie in [0, hd); the column tests are folded into the two limits
-  const unsigned hd0 = (j0 >= 0 && j0 < p.wd) ? (unsigned)p.hd : 0u, hd1 = (j1 >= 0 && j1 < p.wd) ? (unsigned)p.hd : 0u;
-  const unsigned wd = (unsigned)p.wd;
-  const unsigned base = (unsigned)((R::RHO - p.off_h) * p.wd + j0);   // wraps for rows above the window: never used then
-#pragma unroll
-  for (int m = 0; m < 27; ++m) {
-    const unsigned i = (unsigned)(R::RHO + 4 * m - p.off_h);
-    const unsigned off = base + (4u * m) * wd;
-    // v is still re/im swapped: .y is column `line`, .x is column `line + 54`
-    if (i < hd0) y[off] = v[R::n_of(m)].y;
-    if (i < hd1) y[off + HALF] = v[R::n_of(m)].x;
-  }
-}
-
-// ---- pass 1: vertical 27-point DFTs, global -> Z.  Thread (n4 = j = t / 64, line = t % 64 < 54).
-B2C_MATH void pass1(int t, cplx* Z, const Params& p, const double* __restrict__ x) {
-  const int j = t >> 6, line = t & 63;
-  if (line >= HALF) return;
-  cplx v[27];
-  switch (j) {
-    case 0: load_rows<0>(v, p, x, line); break;
-    case 1: load_rows<1>(v, p, x, line); break;
-    case 2: load_rows<2>(v, p, x, line); break;
-    default: load_rows<3>(v, p, x, line); break;
-  }
-  dft27(v);
-  cplx* z = Z + line * LD + NU * j;
+B2C_MATH void p1_store(const cplx* v, const VThread& q, cplx* Z) {
+  cplx* z = Z + q.line * LD + NU * q.j;
 #pragma unroll
   for (int k = 0; k < 27; ++k) z[vpos(k, 0)] = v[k];
+}
+
+// ---- pass 5: inverse vertical DFT27, crop, Z -> global.
+B2C_MATH void p5_load(cplx* v, const VThread& q, const cplx* Z) {
+  const cplx* z = Z + q.line * LD + NU * q.j;
+#pragma unroll
+  for (int k = 0; k < 27; ++k) v[k] = cswap(z[vpos(k, 0)]);
+}
+B2C_MATH void p5_store(const cplx* v, const VThread& q, const Params& p, double* __restrict__ y) {
+  const int j0 = q.line - p.off_w, j1 = q.line + HALF - p.off_w;
+  // output row i = r - off_h must lie in [0, hd); the column tests are folded into the two limits
+  const unsigned hd0 = (j0 >= 0 && j0 < p.wd) ? (unsigned)p.hd : 0u, hd1 = (j1 >= 0 && j1 < p.wd) ? (unsigned)p.hd : 0u;
+  const unsigned wd = (unsigned)p.wd;
+  const int j27 = opaque(27 * q.j);
+  double* yc = y + j0;   // only dereferenced where the column test passed
+#pragma unroll
+  for (int n = 0; n < 27; ++n) {
+    int r = j27 + 4 * n;
+    if (r >= P) r -= P;
+    const unsigned i = (unsigned)(r - p.off_h);   // wraps for rows above the window: fails both tests
+    double* yr = yc + i * wd;
+    // v is still re/im swapped: .y is column `line`, .x is column `line + 54`
+    stg_if(yr, v[n].y, i < hd0);
+    stg_if(yr + HALF, v[n].x, i < hd1);
+  }
 }
 
 struct Pair {   // the two lines and the part flags of horizontal index n27'
@@ -222,23 +272,44 @@ B2C_MATH void pass2(int t, cplx* Z) {
   }
 }
 
-// ---- pass 3: horizontal DFT27, kernel spectrum, inverse DFT27.  Thread (k4', kk = 14 s + u), 224 threads.
+// ---- pass 3: horizontal DFT27, kernel spectrum, inverse DFT27.  Thread (k4' = t / 56, kk = 14 s + u = t % 56).
 // Lines of the 27 points: (4 n) mod 54 for even k4'.  For odd k4' the points live at (4 n + 27) mod 54 =
 // ((4 (n - 7)) mod 54) + 1: the same walk one line further down, started 7 points later.  A cyclic shift of the
 // sequence commutes with the product by the spectrum (it is a phase that the inverse removes), so odd threads
 // just offset their base by one line and every offset below is a compile-time constant.
-B2C_MATH void pass3(int t, cplx* Z, const cplx* __restrict__ kspec) {
-  if (t >= 4 * KK) return;
+B2C_MATH cplx* p3_base(int t, cplx* Z) {
   const int k4 = t / KK, kk = t - k4 * KK;
-  cplx* z = Z + (k4 >> 1) * REGB + kk + ((k4 & 1) ? LD : 0);
-  cplx v[27];
+  return Z + (k4 >> 1) * REGB + kk + ((k4 & 1) ? LD : 0);
+}
+B2C_MATH void p3_load(cplx* v, const cplx* z) {
 #pragma unroll
   for (int n = 0; n < 27; ++n) v[n] = z[((4 * n) % HALF) * LD];
-  dft27(v);
-  const cplx* __restrict__ ks = kspec + (k4 * 27) * KK + kk;
+}
+// v *= kernel spectrum, swapped for the inverse transform.  The 27 values come from L2 (the spectrum is larger than
+// what L1 keeps next to two images' working sets): they are fetched in three volatile groups of nine so that one L2
+// latency covers nine of them -- left to itself the compiler sinks every load next to its use (27 exposed latencies,
+// measured as the top stall of the kernel).
+B2C_MATH cplx ldg_cplx_volatile(const cplx* ptr) {
+#ifdef __CUDA_ARCH__
+  cplx w;
+  asm volatile("ld.global.nc.v2.f64 {%0, %1}, [%2];" : "=d"(w.x), "=d"(w.y) : "l"(ptr));
+  return w;
+#else
+  return *ptr;
+#endif
+}
+B2C_MATH void p3_mul(cplx* v, int t, const cplx* __restrict__ kspec) {
+  const cplx* __restrict__ ks = kspec + t / KK * (27 * KK) + t % KK;
 #pragma unroll
-  for (int k = 0; k < 27; ++k) v[k] = cswap(cmul(v[k], B2C_PFA_LDG(ks + k * KK)));   // swapped for the inverse
-  dft27(v);
+  for (int g = 0; g < 27; g += 9) {
+    cplx w[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) w[k] = ldg_cplx_volatile(ks + (g + k) * KK);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) v[g + k] = cswap(cmul(v[g + k], w[k]));
+  }
+}
+B2C_MATH void p3_store(const cplx* v, cplx* z) {
 #pragma unroll
   for (int n = 0; n < 27; ++n) z[((4 * n) % HALF) * LD] = cswap(v[n]);
 }
@@ -278,23 +349,6 @@ B2C_MATH void pass4(int t, cplx* Z) {
       z0[NU * s + u] = cswap(own[0][s]); z1[NU * s + u] = cswap(own[1][s]);
       z0[REGB + NU * s + u] = cswap(par[0][s]); z1[REGB + NU * s + u] = cswap(par[1][s]);   // u == 0: spare slots, never read
     }
-  }
-}
-
-// ---- pass 5: inverse vertical DFT27, crop, Z -> global.
-B2C_MATH void pass5(int t, const cplx* Z, const Params& p, double* __restrict__ y) {
-  const int j = t >> 6, line = t & 63;
-  if (line >= HALF) return;
-  const cplx* z = Z + line * LD + NU * j;
-  cplx v[27];
-#pragma unroll
-  for (int k = 0; k < 27; ++k) v[k] = cswap(z[vpos(k, 0)]);
-  dft27(v);
-  switch (j) {
-    case 0: store_rows<0>(v, p, y, line); break;
-    case 1: store_rows<1>(v, p, y, line); break;
-    case 2: store_rows<2>(v, p, y, line); break;
-    default: store_rows<3>(v, p, y, line); break;
   }
 }
 

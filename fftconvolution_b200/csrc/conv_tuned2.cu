@@ -1,6 +1,7 @@
-// Family of tuned fused convolution kernels for square periods P x P with P = R1 * R2 (R1 even),
-// the generalisation of conv_tuned108.cu (which stays the hand-tuned (12, 9) member and the
-// headline kernel).  Same seven in-place passes over one shared buffer Z[P/2][LD]:
+// Family of tuned fused convolution kernels for square periods P x P with P = R1 * R2 (R1 even).
+// Period 108 itself (the headline shape) runs the five-pass prime-factor kernel of conv_pfa108.cu; the
+// (12, 9) member here is kept for A/B measurements (B2C_P108=t2).  Seven in-place passes over one shared
+// buffer Z[P/2][LD]:
 //   1 vertical fwd radix-R1 (global -> Z; image columns c and c+P/2 ride one complex transform)
 //   2 vertical fwd radix-R2
 //   3 horizontal fwd radix-R1 with Hermitian unpack (P/2+1 vertical frequencies)
@@ -328,7 +329,7 @@ cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, c
 
 }  // namespace t2
 
-// ---- the menu: square periods with a tuned kernel (108 = 12 x 9 is conv_tuned108.cu) -------------
+// ---- the menu: square periods with a tuned kernel --------------------------------------------------
 #define B2C_T2_MENU(X)                                                                                         \
   X(8, 2) X(10, 2) X(8, 3) X(4, 7) X(8, 4) X(6, 6) X(8, 5) X(6, 7) X(8, 6) X(10, 5) X(6, 9) X(8, 7) X(10, 6) X(8, 8) \
   X(10, 7) X(8, 9) X(10, 8) X(12, 7) X(10, 9) X(12, 8) X(10, 10) X(12, 9) X(14, 8) X(12, 10) X(14, 9) X(16, 8)

@@ -9,8 +9,9 @@
 // points create their scratch lazily with cudaMalloc (kernel spectrum, twiddle tables), so they
 // do not fit those callers.
 //
-// What it does instead: the scratch of the tuned 108 x 108 kernel (conv_tuned108.cu) -- the
-// kernel's spectrum and the table of 108th roots of unity -- lives in ONE file-scope device array
+// What it does instead: the scratch of the period-108 kernel (the (12, 9) member of conv_tuned2.cu,
+// the same kernel the regular entry point runs at that period) -- the kernel's spectrum and the
+// table of 108th roots of unity -- lives in ONE file-scope device array
 // of 98 496 bytes that every GPU loading this library carries until the process exits.  The caller
 // passes only its own input and output buffers.  Any problem whose alias-safe periods fit in 108 on
 // both axes is run at the fixed period 108 x 108; anything larger is refused (B2C_ESIZE).
@@ -36,11 +37,10 @@
 #include "fft_device.cuh"
 
 namespace b2c {
-// conv_tuned108.cu
-int tuned108_occupancy();
-cudaError_t launch_tuned108_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st);
-cudaError_t launch_tuned108_conv(int hs, int ws, int hd, int wd, int off_h, int off_w, const double* d_src,
-                                 double* d_dst, long n, const cplx* kspec, const cplx* tw, int grid, cudaStream_t st);
+// conv_tuned2.cu: kernel spectrum + convolution of a square menu period; allocates nothing
+cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
+                          int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker,
+                          double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
 // capi.cu
 int set_last_error(int code, const char* text);
 }  // namespace b2c
@@ -63,7 +63,6 @@ struct PerDevice {
   bool ready = false;
   unsigned char* base = nullptr;   // device address of g_static_scratch on this device
   int sms = 0;
-  int ctas_per_sm = 0;
 };
 PerDevice g_dev[kMaxDevices];
 std::mutex g_dev_mu;
@@ -97,8 +96,6 @@ int set_up_device(int dev, PerDevice** out) {
     if (e != cudaSuccess) return cuda_fail("cudaStreamSynchronize(root table)", e);
     e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return cuda_fail("cudaDeviceGetAttribute", e);
-    d.ctas_per_sm = b2c::tuned108_occupancy();
-    if (d.ctas_per_sm < 1) return b2c::set_last_error(B2C_ECUDA, "b2c_convolve_batch_device_static: kernel cannot be resident on this device");
     d.ready = true;
   }
   *out = &d;
@@ -160,12 +157,9 @@ extern "C" int b2c_convolve_batch_device_static(int mode, int h_src, int w_src, 
   const b2c::cplx* roots = reinterpret_cast<const b2c::cplx*>(d->base + kRootsOffset);
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   // every call rewrites the whole spectrum before it is read (see the rules at the top of the file)
-  e = b2c::launch_tuned108_kspec(d_kernel, h_kernel, w_kernel, roots, spectrum, st);
-  if (e != cudaSuccess) return cuda_fail("kernel-spectrum launch", e);
-  long grid = (long)d->sms * d->ctas_per_sm;
-  if (grid > n_images) grid = n_images;
-  e = b2c::launch_tuned108_conv(h_src, w_src, ah.n_dst, aw.n_dst, ah.off, aw.off, d_src, d_dst, n_images, spectrum,
-                                roots, (int)grid, st);
-  if (e != cudaSuccess) return cuda_fail("convolution launch", e);
+  int launches = 0;
+  e = b2c::launch_tuned2(kPeriod, h_src, w_src, h_kernel, w_kernel, ah.n_dst, aw.n_dst, ah.off, aw.off, h_src, w_src, 0, 0,
+                         d_src, d_kernel, d_dst, n_images, spectrum, roots, d->sms, st, &launches);
+  if (e != cudaSuccess) return cuda_fail("kernel launch", e);
   return 0;
 }

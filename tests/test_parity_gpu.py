@@ -485,17 +485,21 @@ def test_headline_full_size_properties(b2c, oracle, torch_cuda):
     assert float((d_dst - d_src).abs().max()) < 1e-13
 
 
-def test_tuned_108_kernel_vs_oracle_and_generic(b2c, oracle, torch_cuda):
-    """Plans whose periods are 108 x 108 run on the hand-tuned kernel (conv_tuned108.cu): check it
-    against the oracle, and bit-compare the batch against itself run image by image."""
+@pytest.mark.parametrize("kernel", ["t2", "pfa"])
+def test_tuned_108_kernel_vs_oracle_and_generic(b2c, oracle, torch_cuda, kernel, monkeypatch):
+    """Plans whose periods are 108 x 108 (the headline shape) run on the (12, 9) member of conv_tuned2.cu; the
+    five-pass prime-factor kernel of conv_pfa108.cu is the alternative behind B2C_P108=pfa.  Both against the
+    oracle, and the batch bit-compared against itself run image by image."""
     torch = torch_cuda
+    monkeypatch.setenv("B2C_P108", kernel)
     rng = np.random.default_rng(21)
     cases = [(2, 100, 100, 15, 15), (0, 90, 95, 19, 14), (3, 108, 108, 5, 5), (2, 101, 104, 14, 9),
              (0, 50, 60, 59, 49), (5, 100, 100, 9, 9), (7, 54, 54, 55, 55), (1, 100, 100, 16, 17),
-             (2, 30, 100, 157, 17)]
+             (2, 30, 100, 157, 17), (4, 97, 89, 9, 3)]
     for mode, hs, ws, hk, wk in cases:
         p = b2c.Plan(mode, hs, ws, hk, wk)
-        assert (p.h_fft, p.w_fft) == (108, 108), (mode, hs, ws, hk, wk, p.h_fft, p.w_fft)
+        if mode != b2c.CIRCULAR_SAME:   # (CIRCULAR_SAME reports its own period; it runs as a periodic extension at 108)
+            assert (p.h_fft, p.w_fft) == (108, 108), (mode, hs, ws, hk, wk, p.h_fft, p.w_fft)
         p.set_path(b2c.PATH_FFT)
         n = 5
         src = rng.random((n, hs, ws))
@@ -506,7 +510,7 @@ def test_tuned_108_kernel_vs_oracle_and_generic(b2c, oracle, torch_cuda):
         torch.cuda.synchronize()
         got = d_dst.cpu().numpy()
         for i in range(n):
-            _check(got[i], oracle.convolve_direct8(mode, src[i], ker), ("tuned108", mode, hs, ws, hk, wk, i))
+            _check(got[i], oracle.convolve_direct8(mode, src[i], ker), ("period 108", mode, hs, ws, hk, wk, i))
         g = b2c.Plan(mode, hs, ws, hk, wk)
         g.set_path(b2c.PATH_FFT_GENERIC)
         _check(g.convolve_host(src[0], ker), got[0], ("generic == tuned", mode))
