@@ -531,7 +531,7 @@ def run_b2c_arm(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(),
                 "peak_kind": peak_kind,
-                "kernel": ("b2c::t2::conv_kernel<12,9>" if os.environ.get("B2C_P108") == "t2" else "b2c::pfa::conv_kernel") if (plan.h_fft, plan.w_fft) == (108, 108) else "b2c::conv_shared_kernel", "kernel_ms": avg_ms.value,
+                "kernel": ("b2c::pfa::conv_kernel" if os.environ.get("B2C_P108") == "pfa" else "b2c::t2::conv_kernel<12,9>") if (plan.h_fft, plan.w_fft) == (108, 108) else "b2c::conv_shared_kernel", "kernel_ms": avg_ms.value,
                 "kernel_launches": nl.value, "algorithmic_bytes_per_launch": n_local * ALGO_BYTES_PER_CONV}
 
     cpu_baseline = None
