@@ -48,6 +48,9 @@ size_t tuned2_kspec_bytes(int P);
 cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
                           int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker,
                           double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
+cudaError_t launch_tuned2_perimage(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
+                                   const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kscratch,
+                                   const cplx* tw, int sms, cudaStream_t st, int* launches, long* slots);
 // conv_pfa108.cu
 size_t pfa108_kspec_bytes();
 cudaError_t launch_pfa108(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int hs_in, int ws_in,
@@ -259,14 +262,16 @@ int auto_path(const Plan2D& pl, bool shared) {
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
   if (shared) cost *= 0.5;  // two images per transform
-  const bool tuned = shared && pl.h.P == pl.w.P && (pl.h.P == 108 || tuned2_has(pl.h.P)) && pl.h.fold == 0 &&
-                     pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
+  // per-image kernels on the tuned square kernels: the kernel goes through the forward passes too (measured ~1.35x)
+  const bool tuned_sq = pl.h.P == pl.w.P && tuned2_has(pl.h.P) && pl.h.fold == 0 && pl.w.fold == 0 &&
+                        pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
+  const bool tuned = tuned_sq && (shared || (pl.h.n_ker <= pl.h.P && pl.w.n_ker <= pl.w.P));
   // tuned kernels: 5.6 ps (P <= 80) or 6.5 ps per point of the P x P period (+25 % when only one CTA fits per SM), + 1 ns
   const double pp = (double)pl.h.P * pl.w.P;
   // tuned 1-D kernels (conv_tuned1d.cu): 6.3 ps per point of the period (4.5 ps up to period 512)
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
                       pl.w.fold == 0 && pl.w.kwrap == pl.w.P;
-  const double t_fft = tuned    ? (pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.0e-9
+  const double t_fft = tuned    ? ((pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.0e-9) * (shared ? 1.0 : 1.35)
                        : tuned1 ? (pl.w.P <= 512 ? 4.5e-12 * pl.w.P : 6.3e-12 * pl.w.P + 0.3e-9)
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
@@ -464,6 +469,30 @@ int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const doubl
   return 0;
 }
 
+// Per-image kernels on the same kernels (PERIMG instantiation): the kernel must fit the period un-wrapped.
+bool tuned2_perimage_applies(const b2c_plan* p, const Plan2D& pl) {
+  return p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == pl.w.P && tuned2_has(pl.h.P) && pl.h.fold == 0 &&
+         pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P && pl.h.n_ker <= pl.h.P && pl.w.n_ker <= pl.w.P &&
+         pl.h.src_shift == 0 && pl.w.src_shift == 0;
+}
+
+int run_tuned2_perimage(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const double* d_src, const double* d_ker,
+                        double* d_dst, long n, cudaStream_t st) {
+  long slots = 0;
+  int launches = 0;
+  CUDA_TRY(launch_tuned2_perimage(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
+                                  pl.w.off, nullptr, d_ker, d_dst, n, nullptr, tww.tw, p->ctx->sms, st, &launches, &slots));
+  // one spectrum slot per resident CTA (148 x 2 x 97 KB = 29 MB at period 108: stays in the 126 MB L2)
+  if (int rc = ensure_kspec(p, std::max(work_bytes(pl), (size_t)slots * tuned2_kspec_bytes(pl.h.P)))) return rc;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  CUDA_TRY(g_timer.begin(st, &e0, &e1));
+  CUDA_TRY(launch_tuned2_perimage(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
+                                  pl.w.off, d_src, d_ker, d_dst, n, p->kspec, tww.tw, p->ctx->sms, st, &launches, nullptr));
+  g_launches += launches;
+  CUDA_TRY(g_timer.end(st, e0, e1));
+  return 0;
+}
+
 // 1-D signals (vertical period 1) with a shared kernel and a horizontal period from the 1-D menu
 // (conv_tuned1d.cu).
 bool tuned1d_applies(const b2c_plan* p, const Plan2D& pl, int shared) {
@@ -494,6 +523,7 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
     if (tuned1d_applies(p, p->ext, shared)) return run_tuned1d(p, p->ext, p->tw_ext, d_src, d_ker, d_dst, n, st);
   }
   if (tuned2_applies(p, p->pl, shared)) return run_tuned2(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
+  if (!shared && tuned2_perimage_applies(p, p->pl)) return run_tuned2_perimage(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (tuned1d_applies(p, p->pl, shared)) return run_tuned1d(p, p->pl, p->tw, d_src, d_ker, d_dst, n, st);
   if (work_bytes(pl) > (size_t)p->ctx->smem_optin && pl.h.fold == 0 && pl.w.fold == 0 &&
       p->forced_path != B2C_PATH_FFT_GENERIC && (p->strip_only || big2d_fits(p)))

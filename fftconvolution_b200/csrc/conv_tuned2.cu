@@ -34,6 +34,11 @@ struct Params {
   long n_images;
   const cplx* kspec;  // [P][KLD]: (scrambled horizontal position, half-spectrum vertical frequency kk)
   const cplx* tw;     // exp(-2 pi i k / P)
+  // per-image kernels (PERIMG instantiation): kernel taps [n][hk][wk] with hk, wk <= P, and one spectrum slot of
+  // P * KLD values per CTA in `kscratch` (L2-resident), rewritten for every image
+  const double* ker;
+  int hk, wk;
+  cplx* kscratch;
 };
 
 template <int R> using Big = BigBfly<R>;   // forward DFT of R points in registers (fft_device.cuh)
@@ -66,206 +71,16 @@ struct Geo {
   static constexpr size_t smem_bytes = sizeof(cplx) * (size_t)HALF * LD;
 };
 
-template <int R1, int R2>
-__global__ void __launch_bounds__((Geo<R1, R2>::THREADS), (Geo<R1, R2>::THREADS == 64 ? 8 : Geo<R1, R2>::THREADS == 128 ? 4 : Geo<R1, R2>::smem_bytes <= 110 * 1024 ? 2 : 1))
-conv_kernel(const __grid_constant__ Params p) {
-  typedef Geo<R1, R2> G;
-  constexpr int HALF = G::HALF, H1 = G::H1, NK = G::NK, LD = G::LD, KLD = G::KLD, BPAD = G::BPAD;
-  constexpr int THREADS = G::THREADS, A_LINES = G::A_LINES, A_ROUNDS = G::A_ROUNDS;
-  cplx* Z = reinterpret_cast<cplx*>(b2c_smem_t2);
-  const int t = threadIdx.x;
-  const bool act = t < R2 * A_LINES;
-  const int j = t / A_LINES, la = t - j * A_LINES;   // radix-R1 passes: lanes walk adjacent lines
-  const int jj = act ? j : 0;
-  cplx twr[G::TW_IN_REGS ? R1 : 1];
-  if (G::TW_IN_REGS) {
-#pragma unroll
-    for (int q = 1; q < R1; ++q) twr[q % (G::TW_IN_REGS ? R1 : 1)] = __ldg(&p.tw[jj * q]);
-  }
-#define B2C_TW(q) (G::TW_IN_REGS ? twr[(q) % (G::TW_IN_REGS ? R1 : 1)] : __ldg(&p.tw[jj * (q)]))
-
-  const size_t src_sz = (size_t)p.hs * p.ws, dst_sz = (size_t)p.hd * p.wd;
-  for (long img = blockIdx.x; img < p.n_images; img += gridDim.x) {
-    const double* __restrict__ x = p.src + (size_t)img * src_sz;
-    double* __restrict__ y = p.dst + (size_t)img * dst_sz;
-
-    if (t == 0 && img + gridDim.x < p.n_images) {   // next image -> L2
-      const double* nx = p.src + (size_t)(img + gridDim.x) * src_sz;
-      const unsigned bytes = (unsigned)((src_sz * sizeof(double)) & ~(size_t)15);
-      if ((reinterpret_cast<size_t>(nx) & 15) == 0 && bytes >= 16)
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nx), "r"(bytes) : "memory");
-    }
-
-    // ---- pass 1: vertical forward radix-R1, global -> Z
-#pragma unroll 1
-    for (int rnd = 0; rnd < A_ROUNDS; ++rnd) {
-      const int line = rnd * A_LINES + la;
-      if (act && line < HALF) {
-        const bool c0 = line < p.ws_in, c1 = line + HALF < p.ws_in;
-        cplx v[R1];
-        if ((p.sh_h | p.sh_w) == 0) {
-          const double* xr = x + j * p.ws + line;
-          const int step = R2 * p.ws;
-#pragma unroll
-          for (int q = 0; q < R1; ++q) {
-            const bool in = j + R2 * q < p.hs;
-            v[q].x = (in && c0) ? __ldg(xr + q * step) : 0.0;
-            v[q].y = (in && c1) ? __ldg(xr + q * step + HALF) : 0.0;
-          }
-        } else {   // source extended periodically by (sh_h, sh_w) samples in front
-          int sc0 = line - p.sh_w, sc1 = line + HALF - p.sh_w;
-          if (sc0 < 0) sc0 += p.ws;
-          if (sc1 < 0) sc1 += p.ws;
-#pragma unroll
-          for (int q = 0; q < R1; ++q) {
-            const int r = j + R2 * q;
-            int sr = r - p.sh_h;
-            if (sr < 0) sr += p.hs;
-            const bool in = r < p.hs_in;
-            v[q].x = (in && c0) ? __ldg(x + sr * p.ws + sc0) : 0.0;
-            v[q].y = (in && c1) ? __ldg(x + sr * p.ws + sc1) : 0.0;
-          }
-        }
-        Big<R1>::run(v);
-        cplx* z = Z + line * LD + j;
-        z[0] = v[0];
-#pragma unroll
-        for (int q = 1; q < R1; ++q) z[R2 * q] = cmul(v[q], B2C_TW(q));
-      }
-    }
-    __syncthreads();
-
-    // ---- pass 2: vertical forward radix-R2 (task = block pb of line `line`)
-#pragma unroll 1
-    for (int task = t; task < R1 * BPAD; task += THREADS) {
-      const int pb = task / BPAD, line = task - pb * BPAD;
-      if (line >= HALF) continue;
-      cplx* z = Z + line * LD + R2 * pb;
-      cplx v[R2];
-#pragma unroll
-      for (int s = 0; s < R2; ++s) v[s] = z[s];
-      Big<R2>::run(v);
-#pragma unroll
-      for (int s = 0; s < R2; ++s) z[s] = v[s];
-    }
-    __syncthreads();
-
-    // ---- pass 3: horizontal, Hermitian unpack + forward radix-R1
-#pragma unroll 1
-    for (int rnd = 0; rnd < A_ROUNDS; ++rnd) {
-      const int kk = rnd * A_LINES + la;
-      if (act && kk < NK) {
-        const int rep = G::rep_of(kk), par = G::par_of(kk);
-        const bool self = G::self_of(kk);
-        cplx* zr = Z + j * LD + rep;
-        cplx* zp = Z + j * LD + par;
-        cplx v[R1];
-#pragma unroll
-        for (int q = 0; q < H1; ++q) {
-          const cplx z1 = zr[R2 * q * LD];
-          const cplx z2 = self ? z1 : zp[R2 * q * LD];
-          v[q] = make_double2(z1.x + z2.x, z1.y - z2.y);          // 2 * FFT(column c)       at this frequency
-          v[q + H1] = make_double2(z1.y + z2.y, z2.x - z1.x);     // 2 * FFT(column c + P/2)
-        }
-        Big<R1>::run(v);
-        zr[0] = v[0];
-#pragma unroll
-        for (int q = 1; q < H1; ++q) zr[R2 * q * LD] = cmul(v[q], B2C_TW(q));
-#pragma unroll
-        for (int q = H1; q < R1; ++q) zp[R2 * (q - H1) * LD] = cmul(v[q], B2C_TW(q));
-      }
-    }
-    __syncthreads();
-
-    // ---- pass 4: horizontal radix-R2 forward, spectrum product, radix-R2 backward
-#pragma unroll 1
-    for (int task = t; task < R1 * BPAD; task += THREADS) {
-      const int pb = task / BPAD, kk = task - pb * BPAD;
-      if (kk >= NK) continue;
-      const int col = pb < H1 ? G::rep_of(kk) : G::par_of(kk);
-      cplx* z = Z + (R2 * (pb < H1 ? pb : pb - H1)) * LD + col;
-      const cplx* __restrict__ ks = p.kspec + (R2 * pb) * KLD + kk;
-      cplx v[R2];
-#pragma unroll
-      for (int s = 0; s < R2; ++s) v[s] = z[s * LD];
-      Big<R2>::run(v);
-#pragma unroll
-      for (int s = 0; s < R2; ++s) v[s] = cswap(cmul(v[s], __ldg(ks + s * KLD)));   // product, swapped for the inverse
-      Big<R2>::run(v);
-#pragma unroll
-      for (int s = 0; s < R2; ++s) z[s * LD] = cswap(v[s]);
-    }
-    __syncthreads();
-
-    // ---- pass 5: horizontal backward radix-R1, repack two real columns into one complex line
-#pragma unroll 1
-    for (int rnd = 0; rnd < A_ROUNDS; ++rnd) {
-      const int kk = rnd * A_LINES + la;
-      if (act && kk < NK) {
-        const int rep = G::rep_of(kk), par = G::par_of(kk);
-        const bool self = G::self_of(kk);
-        cplx* zr = Z + j * LD + rep;
-        cplx* zp = Z + j * LD + par;
-        cplx v[R1];
-        v[0] = cswap(zr[0]);
-#pragma unroll
-        for (int q = 1; q < H1; ++q) v[q] = cswap(cmulc(zr[R2 * q * LD], B2C_TW(q)));
-#pragma unroll
-        for (int q = H1; q < R1; ++q) v[q] = cswap(cmulc(zp[R2 * (q - H1) * LD], B2C_TW(q)));
-        Big<R1>::run(v);
-#pragma unroll
-        for (int q = 0; q < H1; ++q) {
-          const cplx y1 = cswap(v[q]), y2 = cswap(v[q + H1]);
-          zr[R2 * q * LD] = make_double2(y1.x - y2.y, y1.y + y2.x);              // Y1 + i*Y2 at +freq
-          if (!self) zp[R2 * q * LD] = make_double2(y1.x + y2.y, y2.x - y1.y);   // conj(Y1) + i*conj(Y2) at -freq
-        }
-      }
-    }
-    __syncthreads();
-
-    // ---- pass 6: vertical backward radix-R2
-#pragma unroll 1
-    for (int task = t; task < R1 * BPAD; task += THREADS) {
-      const int pb = task / BPAD, line = task - pb * BPAD;
-      if (line >= HALF) continue;
-      cplx* z = Z + line * LD + R2 * pb;
-      cplx v[R2];
-#pragma unroll
-      for (int s = 0; s < R2; ++s) v[s] = cswap(z[s]);
-      Big<R2>::run(v);
-#pragma unroll
-      for (int s = 0; s < R2; ++s) z[s] = cswap(v[s]);
-    }
-    __syncthreads();
-
-    // ---- pass 7: vertical backward radix-R1, crop, Z -> global
-#pragma unroll 1
-    for (int rnd = 0; rnd < A_ROUNDS; ++rnd) {
-      const int line = rnd * A_LINES + la;
-      if (act && line < HALF) {
-        const cplx* z = Z + line * LD + j;
-        cplx v[R1];
-        v[0] = cswap(z[0]);
-#pragma unroll
-        for (int q = 1; q < R1; ++q) v[q] = cswap(cmulc(z[R2 * q], B2C_TW(q)));
-        Big<R1>::run(v);   // results: re/im swapped => v[q].y is column `line`, v[q].x is column `line + P/2`
-        const int j0 = line - p.off_w, j1 = line + HALF - p.off_w;
-        const bool o0 = j0 >= 0 && j0 < p.wd, o1 = j1 >= 0 && j1 < p.wd;
-        const int i0 = j - p.off_h;
-        double* yr = y + i0 * p.wd + j0;
-        const int step = R2 * p.wd;
-#pragma unroll
-        for (int q = 0; q < R1; ++q) {
-          const bool in = (unsigned)(i0 + R2 * q) < (unsigned)p.hd;
-          if (in && o0) yr[q * step] = v[q].y;
-          if (in && o1) yr[q * step + HALF] = v[q].x;
-        }
-      }
-    }
-    // no barrier: the next image's pass 1 writes exactly the slots this thread just read
-  }
-#undef B2C_TW
-}
+#define B2C_T2_PERIMG 0
+#define B2C_T2_KERNEL conv_kernel
+#include "conv_tuned2_kernel.inc"
+#undef B2C_T2_PERIMG
+#undef B2C_T2_KERNEL
+#define B2C_T2_PERIMG 1
+#define B2C_T2_KERNEL conv_kernel_perimage
+#include "conv_tuned2_kernel.inc"
+#undef B2C_T2_PERIMG
+#undef B2C_T2_KERNEL
 
 // Kernel spectrum K[pos][kk] = 0.5/(P*P) * DFT2(kernel)[u(kk)][v(pos)], straight from the taps.
 template <int R1, int R2>
@@ -327,6 +142,23 @@ cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, c
   return cudaGetLastError();
 }
 
+// per-image kernels: *grid_out (when non-null) only asks for the grid this launch would use, i.e. how many
+// spectrum slots `kscratch` needs
+template <int R1, int R2>
+cudaError_t run_perimage(const Params& p, int sms, cudaStream_t st, int* launches, long* grid_out) {
+  typedef Geo<R1, R2> G;
+  int occ = 0;
+  cudaFuncSetAttribute(conv_kernel_perimage<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_kernel_perimage<R1, R2>, G::THREADS, G::smem_bytes);
+  if (occ < 1) return cudaErrorLaunchOutOfResources;
+  long grid = (long)sms * occ;
+  if (grid_out) { *grid_out = grid; return cudaSuccess; }
+  if (grid > p.n_images) grid = p.n_images;
+  conv_kernel_perimage<R1, R2><<<(int)grid, G::THREADS, G::smem_bytes, st>>>(p);
+  ++*launches;
+  return cudaGetLastError();
+}
+
 }  // namespace t2
 
 // ---- the menu: square periods with a tuned kernel --------------------------------------------------
@@ -354,8 +186,27 @@ cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd,
   p.hs = hs; p.ws = ws; p.hd = hd; p.wd = wd; p.off_h = off_h; p.off_w = off_w;
   p.hs_in = hs_in; p.ws_in = ws_in; p.sh_h = sh_h; p.sh_w = sh_w;
   p.src = d_src; p.dst = d_dst; p.n_images = n; p.kspec = kspec; p.tw = tw;
+  p.ker = nullptr; p.hk = hk; p.wk = wk; p.kscratch = nullptr;
   switch (P) {
 #define X(a, b) case (a) * (b): return t2::run<a, b>(p, d_ker, hk, wk, sms, st, launches);
+    B2C_T2_MENU(X)
+#undef X
+  }
+  return cudaErrorInvalidValue;
+}
+
+// Per-image kernels on a square menu period (kernel extents <= P): `kscratch` holds one spectrum slot of
+// tuned2_kspec_bytes(P) per CTA of the launch; with d_src == nullptr only *slots is filled in (nothing runs).
+cudaError_t launch_tuned2_perimage(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
+                                   const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kscratch,
+                                   const cplx* tw, int sms, cudaStream_t st, int* launches, long* slots) {
+  t2::Params p;
+  p.hs = hs; p.ws = ws; p.hd = hd; p.wd = wd; p.off_h = off_h; p.off_w = off_w;
+  p.hs_in = hs; p.ws_in = ws; p.sh_h = 0; p.sh_w = 0;
+  p.src = d_src; p.dst = d_dst; p.n_images = n; p.kspec = nullptr; p.tw = tw;
+  p.ker = d_ker; p.hk = hk; p.wk = wk; p.kscratch = kscratch;
+  switch (P) {
+#define X(a, b) case (a) * (b): return t2::run_perimage<a, b>(p, sms, st, launches, d_src ? nullptr : slots);
     B2C_T2_MENU(X)
 #undef X
   }

@@ -603,3 +603,51 @@ def test_tuned_square_period_family_vs_oracle(b2c, oracle, torch_cuda):
             _check(g.convolve_host(src[1], ker), got[1], ("generic == tuned2", P, mode))
             p.destroy(); g.destroy()
     assert hit == set(menu), sorted(set(menu) - hit)
+
+
+def test_tuned_square_period_family_with_per_image_kernels(b2c, oracle, torch_cuda):
+    """Per-image kernels on every square menu period (16 ... 128, 108 included): each image's kernel runs through the
+    forward passes on its own and its spectrum is parked in the CTA's slot (conv_tuned2.cu, PERIMG).  More images
+    than resident CTAs would need thousands of them; instead the batch is odd, kernels differ in size up to the
+    period itself, and neighbouring images and kernels differ in magnitude by many decades (source and kernel are
+    transformed separately, like convolution_fftw.h:190-191, so 1e-12 must hold without any balancing)."""
+    torch = torch_cuda
+    rng = np.random.default_rng(43)
+    menu = [16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128]
+    hit = set()
+    for P in menu:
+        shapes = [(b2c.LINEAR_SAME, P - 4, P - 7, 9, 15), (b2c.LINEAR_FULL, P - 9, P - 13, 10, 14),
+                  (b2c.CIRCULAR_FULL, P // 2, P // 2 + 1, P // 2 + 1, P // 2), (b2c.LINEAR_VALID, P, P - 3, 5, 3)]
+        for mode, hs, ws, hk, wk in shapes:
+            if min(hs, ws, hk, wk) < 1:
+                continue
+            p = b2c.Plan(mode, hs, ws, hk, wk)
+            if (p.h_fft, p.w_fft) != (P, P):
+                p.destroy()
+                continue
+            hit.add(P)
+            p.set_path(b2c.PATH_FFT)
+            n = 5
+            src = rng.random((n, hs, ws)) * 10.0 ** rng.uniform(-5, 5, size=(n, 1, 1))
+            ker = (rng.random((n, hk, wk)) - 0.4) * 10.0 ** rng.uniform(-5, 5, size=(n, 1, 1))
+            d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+            d_dst = torch.full((n, p.h_dst, p.w_dst), float("nan"), dtype=torch.float64, device="cuda")
+            p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 0, d_dst.data_ptr(), n, 0)
+            torch.cuda.synchronize()
+            got = d_dst.cpu().numpy()
+            for i in range(n):
+                _check(got[i], oracle.convolve_direct8(mode, src[i], ker[i]), ("tuned2 per-image", P, mode, hs, ws, hk, wk, i))
+            p.destroy()
+    assert hit == set(menu), sorted(set(menu) - hit)
+    # many more images than CTAs: every CTA reuses its spectrum slot many times (headline shape, per-image kernels)
+    n, hs, hk = 1500, 100, 15
+    src, ker = rng.random((n, hs, hs)), rng.random((n, hk, hk))
+    p = b2c.Plan(b2c.LINEAR_SAME, hs, hs, hk, hk)
+    d_src, d_ker = torch.from_numpy(src).cuda(), torch.from_numpy(ker).cuda()
+    d_dst = torch.full((n, hs, hs), float("nan"), dtype=torch.float64, device="cuda")
+    p.convolve_batch_device(d_src.data_ptr(), d_ker.data_ptr(), 0, d_dst.data_ptr(), n, 0)
+    torch.cuda.synchronize()
+    got = d_dst.cpu().numpy()
+    for i in (0, 1, 295, 296, 297, 700, 1498, 1499):
+        _check(got[i], oracle.convolve_direct8(b2c.LINEAR_SAME, src[i], ker[i]), ("per-image slots reused", i))
+    p.destroy()
