@@ -508,6 +508,8 @@ def run_b2c_arm(args):
         jobs = [
             ("configs[2]: 100x100 (*) 100x100 CIRCULAR_FULL, per-image kernels, %d per GPU" % N3,
              b2c.CIRCULAR_FULL, 100, 100, 100, 100, N3, False, SEED3, 5, 8 * (2 * 100 * 100 + 199 * 199)),
+            ("configs[1] shape with per-image kernels: 100x100 (*) 15x15 LINEAR_SAME, %d per GPU" % (2 * N3),
+             b2c.LINEAR_SAME, 100, 100, 15, 15, 2 * N3, False, SEED3, 10, 8 * (2 * 100 * 100 + 15 * 15)),
             ("configs[3]: 1x4096 (*) 1x255 LINEAR_SAME rows, shared kernel, %d per GPU" % N4,
              b2c.LINEAR_SAME, 1, 4096, 1, 255, N4, True, SEED4, 20, 8 * (4096 + 4096)),
             ("configs[3]: 4096x1 (*) 255x1 LINEAR_SAME columns, shared kernel, %d per GPU" % N4,

@@ -259,6 +259,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   if (pl.h.n_dst >= 8) t_direct = std::max(bytes / (pl.h.n_dst >= 64 ? 3.5e12 : 2.8e12), fma / 5.2e12) + per_image;
   else t_direct = bytes / 3.4e12 + fma / 4.5e12 + (shared ? std::min(2e-9, bytes * 1.25e-13) : per_image);   // long rows: one tile per CTA
   if (pl.h.n_ker > 16) t_direct *= 4.0;
+  if (pl.mode == B2C_CIRCULAR_SAME) t_direct *= 1.35;   // wrapped source indices (profiles/r02_crossover_all_modes.csv)
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
   if (shared) cost *= 0.5;  // two images per transform
@@ -271,7 +272,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   // tuned 1-D kernels (conv_tuned1d.cu): 6.3 ps per point of the period (4.5 ps up to period 512)
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
                       pl.w.fold == 0 && pl.w.kwrap == pl.w.P;
-  const double t_fft = tuned    ? ((pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.0e-9) * (shared ? 1.0 : 1.35)
+  const double t_fft = tuned    ? ((pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.5e-9) * (shared ? 1.0 : 1.35)
                        : tuned1 ? (pl.w.P <= 512 ? 4.5e-12 * pl.w.P : 6.3e-12 * pl.w.P + 0.3e-9)
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
