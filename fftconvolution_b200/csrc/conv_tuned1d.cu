@@ -28,6 +28,9 @@ namespace t1 {
 #ifndef B2C_T1_POW
 #define B2C_T1_POW 1
 #endif
+#ifndef B2C_T1_PREFETCH
+#define B2C_T1_PREFETCH 1
+#endif
 
 struct Params {
   int ns, nd, off;          // signal length, result length, crop offset
@@ -246,6 +249,12 @@ __global__ void __launch_bounds__((Geo<P, R0, R1, R2, R3>::THREADS), (Geo<P, R0,
   for (long pr = blockIdx.x; pr < pairs; pr += gridDim.x) {
     const double* a = p.src + (size_t)(2 * pr) * p.ns;
     const bool two = 2 * pr + 1 < p.n_signals;
+#if B2C_T1_PREFETCH
+    if (threadIdx.x == 0 && pr + gridDim.x < pairs) {   // next pair -> L2: its first pass meets L2 latency, not HBM latency
+      const long nxt = 2 * (pr + gridDim.x);
+      l2_prefetch(p.src + (size_t)nxt * p.ns, (size_t)(nxt + 1 < p.n_signals ? 2 : 1) * p.ns * sizeof(double));
+    }
+#endif
     const double* b2 = two ? a + p.ns : nullptr;
     double* da = p.dst + (size_t)(2 * pr) * p.nd;
     double* db = two ? da + p.nd : nullptr;

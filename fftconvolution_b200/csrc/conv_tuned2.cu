@@ -43,6 +43,28 @@ struct Params {
 
 template <int R> using Big = BigBfly<R>;   // forward DFT of R points in registers (fft_device.cuh)
 
+// Predicated global accesses of passes 1 and 7.  B2C_T2_ASM_PRED=1: one predicated instruction each (inline PTX)
+// instead of what the compiler makes of a conditional expression (select / branch per element).
+#ifndef B2C_T2_ASM_PRED
+#define B2C_T2_ASM_PRED 0
+#endif
+__device__ __forceinline__ double ldg_if(const double* ptr, bool on) {
+  double v;
+  asm volatile("{\n .reg .pred p;\n setp.ne.u32 p, %2, 0;\n mov.f64 %0, 0d0000000000000000;\n @p ld.global.nc.f64 %0, [%1];\n}"
+               : "=d"(v) : "l"(ptr), "r"((unsigned)on));
+  return v;
+}
+__device__ __forceinline__ void stg_if(double* ptr, double v, bool on) {
+  asm volatile("{\n .reg .pred p;\n setp.ne.u32 p, %2, 0;\n @p st.global.f64 [%0], %1;\n}" ::"l"(ptr), "d"(v), "r"((unsigned)on) : "memory");
+}
+#if B2C_T2_ASM_PRED
+#define B2C_T2_LDG_IF(ptr, on) ldg_if(ptr, on)
+#define B2C_T2_STG_IF(ptr, val, on) stg_if(ptr, val, on)
+#else
+#define B2C_T2_LDG_IF(ptr, on) ((on) ? __ldg(ptr) : 0.0)
+#define B2C_T2_STG_IF(ptr, val, on) do { if (on) *(ptr) = (val); } while (0)
+#endif
+
 template <int R1, int R2>
 struct Geo {
   static constexpr int P = R1 * R2;
