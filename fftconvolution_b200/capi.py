@@ -21,7 +21,7 @@ PATH_AUTO, PATH_FFT, PATH_DIRECT, PATH_FFT_GENERIC = 0, 1, 2, 3
 SYMBOLS = [
     "b2c_plan_create", "b2c_plan_query", "b2c_plan_info", "b2c_plan_set_path", "b2c_plan_destroy",
     "b2c_convolve_host", "b2c_convolve_batch_host", "b2c_convolve_batch_device",
-    "b2c_convolve_batch_device_static",
+    "b2c_convolve_batch_device_static", "b2c_convolve_batch_device_f32", "b2c_convolve_batch_device_c64",
     "b2c_find_closest_factor", "b2c_smooth_size", "b2c_partition", "b2c_checksum_device",
     "b2c_fill_uniform_device", "b2c_multi_convolve_batch_host", "b2c_host_alloc", "b2c_host_free", "b2c_set_device",
     "b2c_launch_count", "b2c_kernel_timer", "b2c_kernel_timer_read", "b2c_last_error", "b2c_version",
@@ -65,6 +65,8 @@ def lib():
     L.b2c_convolve_batch_device.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_long, c_void_p]
     L.b2c_convolve_batch_device_static.argtypes = [c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                                    c_long, c_void_p]
+    L.b2c_convolve_batch_device_f32.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_long, c_void_p]
+    L.b2c_convolve_batch_device_c64.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_long, c_void_p]
     L.b2c_find_closest_factor.argtypes = [c_int]
     L.b2c_smooth_size.argtypes = [c_int]
     L.b2c_partition.argtypes = [c_long, c_int, c_int, lp, lp]

@@ -78,6 +78,16 @@ class Plan:
         check(lib().b2c_convolve_batch_device(self._h, int(d_src), int(d_kernel), int(shared), int(d_dst),
                                               int(n), ctypes.c_void_p(int(stream))))
 
+    def convolve_batch_device_f32(self, d_src, d_kernel, shared, d_dst, n, stream=0):
+        """float32 device buffers in and out, FP64 arithmetic (b2c_convolve_batch_device_f32)."""
+        check(lib().b2c_convolve_batch_device_f32(self._h, int(d_src), int(d_kernel), int(shared), int(d_dst),
+                                                  int(n), ctypes.c_void_p(int(stream))))
+
+    def convolve_batch_device_c64(self, d_src, d_kernel, shared, d_dst, n, stream=0):
+        """complex128 (interleaved) device buffers, complex kernel (b2c_convolve_batch_device_c64)."""
+        check(lib().b2c_convolve_batch_device_c64(self._h, int(d_src), int(d_kernel), int(shared), int(d_dst),
+                                                  int(n), ctypes.c_void_p(int(stream))))
+
     def destroy(self):
         if self._h:
             check(lib().b2c_plan_destroy(self._h))

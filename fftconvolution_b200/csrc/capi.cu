@@ -61,6 +61,10 @@ cudaError_t launch_fill_uniform(double* d, long n, unsigned long long seed, long
 cudaError_t launch_balance(const double* d_src, long src_sz, const double* d_ker, long ker_sz, long ker_stride, long n,
                            double* d_alpha, unsigned long long* d_maxima, int sms, cudaStream_t st);
 cudaError_t launch_checksum(const double* d, long n, unsigned long long* d_out3, cudaStream_t st);
+cudaError_t launch_widen(const float* in, double* out, long n, cudaStream_t st);
+cudaError_t launch_narrow(const double* in, float* out, long n, cudaStream_t st);
+cudaError_t launch_split_complex(const double* in, double* re, double* im, long n, cudaStream_t st);
+cudaError_t launch_combine_complex(const double* a, const double* b, double sign, double* out, int part, long n, cudaStream_t st);
 }  // namespace b2c
 
 using namespace b2c;
@@ -231,6 +235,9 @@ struct b2c_plan {
   double* d_dst[kPipe] = {nullptr, nullptr, nullptr};
   long pipe_chunk = 0;
   int pipe_shared = -1;
+  // staging of the single-precision / complex adapters (b2c_convolve_batch_device_f32 / _c64), grown on demand
+  double* adapt = nullptr;
+  size_t adapt_bytes = 0;
   cudaStream_t s_h2d = nullptr, s_cmp = nullptr, s_d2h = nullptr;
   cudaEvent_t ev_h2d[kPipe], ev_cmp[kPipe], ev_d2h[kPipe];
   bool pipe_ready = false;
@@ -808,6 +815,7 @@ int b2c_plan_destroy(b2c_plan* p) {
   if (p->alpha) cudaFree(p->alpha);
   if (p->d_one) cudaFree(p->d_one);
   if (p->h_one) cudaFreeHost(p->h_one);
+  if (p->adapt) cudaFree(p->adapt);
   free_pipe(p);
   if (p->pipe_ready) {
     for (int i = 0; i < kPipe; ++i) {
@@ -830,6 +838,91 @@ int b2c_convolve_batch_device(b2c_plan* p, const double* d_src, const double* d_
   if (effective_path(p, kernel_is_shared) == B2C_PATH_DIRECT)
     return run_direct_path(p, d_src, d_kernel, kernel_is_shared, d_dst, n_images, st);
   return run_fft_path(p, d_src, d_kernel, kernel_is_shared, d_dst, n_images, st);
+}
+
+// ---- single-precision and complex inputs (the reference is double-real only,
+// convolution_fftw.h:216).  Adapters around the FP64 real engine: the batch is processed in chunks through a staging
+// buffer the plan owns; all arithmetic stays FP64.
+namespace {
+int ensure_adapt(b2c_plan* p, size_t bytes) {
+  if (p->adapt && p->adapt_bytes >= bytes) return 0;
+  if (p->adapt) CUDA_TRY(cudaFree(p->adapt));
+  p->adapt = nullptr; p->adapt_bytes = 0;
+  CUDA_TRY(cudaMalloc(&p->adapt, bytes));
+  p->adapt_bytes = bytes;
+  return 0;
+}
+long adapt_chunk(long n, size_t doubles_per_image) {
+  const size_t budget = (size_t)256 << 20;   // bytes of staging per chunk
+  long m = (long)std::max<size_t>(2, budget / (8 * std::max<size_t>(doubles_per_image, 1)));
+  m = std::min(m, n);
+  if (m > 1 && (m & 1)) --m;   // keep image pairs together
+  return m;
+}
+}  // namespace
+
+int b2c_convolve_batch_device_f32(b2c_plan* p, const float* d_src, const float* d_kernel, int kernel_is_shared, float* d_dst,
+                                  long n_images, void* cuda_stream) {
+  if (!p) return fail(B2C_EINVAL, "b2c_convolve_batch_device_f32: null plan");
+  if (n_images < 0) return fail(B2C_EINVAL, "b2c_convolve_batch_device_f32: negative batch");
+  if (p->pl.empty || n_images == 0) return 0;
+  if (!d_src || !d_kernel || !d_dst) return fail(B2C_EINVAL, "b2c_convolve_batch_device_f32: null buffer");
+  const Plan2D& pl = p->pl;
+  const size_t sn = (size_t)pl.h.n_src * pl.w.n_src, kn = (size_t)pl.h.n_ker * pl.w.n_ker, dn = (size_t)pl.h.n_dst * pl.w.n_dst;
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  const long m = adapt_chunk(n_images, sn + dn + (kernel_is_shared ? 0 : kn));
+  auto even = [](size_t x) { return (x + 1) & ~(size_t)1; };   // sub-buffers stay 16-byte aligned
+  if (int rc = ensure_adapt(p, 8 * (even(sn * m) + even(dn * m) + kn * (kernel_is_shared ? 1 : m)))) return rc;
+  double* ds = p->adapt;
+  double* dd = ds + even(sn * m);
+  double* dk = dd + even(dn * m);
+  if (kernel_is_shared) CUDA_TRY(launch_widen(d_kernel, dk, (long)kn, st));
+  for (long done = 0; done < n_images; done += m) {
+    const long c = std::min(m, n_images - done);
+    CUDA_TRY(launch_widen(d_src + sn * done, ds, (long)(sn * c), st));
+    if (!kernel_is_shared) CUDA_TRY(launch_widen(d_kernel + kn * done, dk, (long)(kn * c), st));
+    if (int rc = b2c_convolve_batch_device(p, ds, dk, kernel_is_shared, dd, c, st)) return rc;
+    CUDA_TRY(launch_narrow(dd, d_dst + dn * done, (long)(dn * c), st));
+    g_launches += kernel_is_shared ? 2 : 3;
+  }
+  return 0;
+}
+
+int b2c_convolve_batch_device_c64(b2c_plan* p, const double* d_src, const double* d_kernel, int kernel_is_shared, double* d_dst,
+                                  long n_images, void* cuda_stream) {
+  if (!p) return fail(B2C_EINVAL, "b2c_convolve_batch_device_c64: null plan");
+  if (n_images < 0) return fail(B2C_EINVAL, "b2c_convolve_batch_device_c64: negative batch");
+  if (p->pl.empty || n_images == 0) return 0;
+  if (!d_src || !d_kernel || !d_dst) return fail(B2C_EINVAL, "b2c_convolve_batch_device_c64: null buffer");
+  const Plan2D& pl = p->pl;
+  const size_t sn = (size_t)pl.h.n_src * pl.w.n_src, kn = (size_t)pl.h.n_ker * pl.w.n_ker, dn = (size_t)pl.h.n_dst * pl.w.n_dst;
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  const long m = adapt_chunk(n_images, 2 * (sn + dn) + (kernel_is_shared ? 0 : 2 * kn));
+  const size_t kc = kn * (kernel_is_shared ? 1 : m);
+  auto even = [](size_t x) { return (x + 1) & ~(size_t)1; };   // sub-buffers stay 16-byte aligned
+  if (int rc = ensure_adapt(p, 8 * (2 * even(sn * m) + 2 * even(dn * m) + 2 * even(kc)))) return rc;
+  double* a = p->adapt;        // Re(src), Im(src)
+  double* b = a + even(sn * m);
+  double* t1 = b + even(sn * m);     // two real results at a time
+  double* t2 = t1 + even(dn * m);
+  double* c = t2 + even(dn * m);     // Re(kernel), Im(kernel)
+  double* d = c + even(kc);
+  if (kernel_is_shared) CUDA_TRY(launch_split_complex(d_kernel, c, d, (long)kn, st));
+  for (long done = 0; done < n_images; done += m) {
+    const long cnt = std::min(m, n_images - done);
+    CUDA_TRY(launch_split_complex(d_src + 2 * sn * done, a, b, (long)(sn * cnt), st));
+    if (!kernel_is_shared) CUDA_TRY(launch_split_complex(d_kernel + 2 * kn * done, c, d, (long)(kn * cnt), st));
+    double* out = d_dst + 2 * dn * done;
+    // (a + ib) (*) (c + id) = (a(*)c - b(*)d) + i (a(*)d + b(*)c): four real convolutions, no cancellation tricks
+    if (int rc = b2c_convolve_batch_device(p, a, c, kernel_is_shared, t1, cnt, st)) return rc;
+    if (int rc = b2c_convolve_batch_device(p, b, d, kernel_is_shared, t2, cnt, st)) return rc;
+    CUDA_TRY(launch_combine_complex(t1, t2, -1.0, out, 0, (long)(dn * cnt), st));
+    if (int rc = b2c_convolve_batch_device(p, a, d, kernel_is_shared, t1, cnt, st)) return rc;
+    if (int rc = b2c_convolve_batch_device(p, b, c, kernel_is_shared, t2, cnt, st)) return rc;
+    CUDA_TRY(launch_combine_complex(t1, t2, 1.0, out, 1, (long)(dn * cnt), st));
+    g_launches += kernel_is_shared ? 3 : 4;
+  }
+  return 0;
 }
 
 int b2c_convolve_host(b2c_plan* p, const double* src, const double* kernel, double* dst) {

@@ -108,4 +108,46 @@ cudaError_t launch_checksum(const double* d, long n, unsigned long long* d_out3,
   return cudaGetLastError();
 }
 
+// ---- single-precision and complex inputs: thin adapters around the FP64 real engine ----------
+__global__ void widen_kernel(const float* __restrict__ in, double* __restrict__ out, long n) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = (double)__ldg(in + i);
+}
+__global__ void narrow_kernel(const double* __restrict__ in, float* __restrict__ out, long n) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = (float)in[i];
+}
+// interleaved complex -> two real planes
+__global__ void split_complex_kernel(const double2* __restrict__ in, double* __restrict__ re, double* __restrict__ im, long n) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double2 v = __ldg(in + i);
+    re[i] = v.x; im[i] = v.y;
+  }
+}
+// out[i].part = a[i] + sign * b[i]   (part 0: real, 1: imaginary; the other part is left as it is)
+__global__ void combine_complex_kernel(const double* __restrict__ a, const double* __restrict__ b, double sign, double* __restrict__ out,
+                                       int part, long n) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[2 * i + part] = a[i] + sign * b[i];
+}
+
+static int grid_for(long n) { return (int)((n + 255) / 256 < 148L * 16 ? (n + 255) / 256 : 148L * 16); }
+cudaError_t launch_widen(const float* in, double* out, long n, cudaStream_t st) {
+  if (n > 0) widen_kernel<<<grid_for(n), 256, 0, st>>>(in, out, n);
+  return cudaGetLastError();
+}
+cudaError_t launch_narrow(const double* in, float* out, long n, cudaStream_t st) {
+  if (n > 0) narrow_kernel<<<grid_for(n), 256, 0, st>>>(in, out, n);
+  return cudaGetLastError();
+}
+cudaError_t launch_split_complex(const double* in, double* re, double* im, long n, cudaStream_t st) {
+  if (n > 0) split_complex_kernel<<<grid_for(n), 256, 0, st>>>(reinterpret_cast<const double2*>(in), re, im, n);
+  return cudaGetLastError();
+}
+cudaError_t launch_combine_complex(const double* a, const double* b, double sign, double* out, int part, long n, cudaStream_t st) {
+  if (n > 0) combine_complex_kernel<<<grid_for(n), 256, 0, st>>>(a, b, sign, out, part, n);
+  return cudaGetLastError();
+}
+
 }  // namespace b2c

@@ -78,6 +78,16 @@ int b2c_convolve_batch_host(b2c_plan* plan, const double* src, const double* ker
 int b2c_convolve_batch_device(b2c_plan* plan, const double* d_src, const double* d_kernel,
                               int kernel_is_shared, double* d_dst, long n_images, void* cuda_stream);
 
+/* No counterpart in the reference (it is double-real only, convolution_fftw.h:216): the same
+ * batch with SINGLE-PRECISION device buffers (float in, float out; the arithmetic stays FP64: inputs are widened and
+ * the result narrowed through a staging buffer the plan owns, in chunks of at most 256 MB), and with COMPLEX
+ * double-precision buffers (interleaved re, im; kernel complex too; computed as four real convolutions).  Layouts
+ * otherwise as b2c_convolve_batch_device; asynchronous on `cuda_stream`; the first call may allocate the staging. */
+int b2c_convolve_batch_device_f32(b2c_plan* plan, const float* d_src, const float* d_kernel, int kernel_is_shared,
+                                  float* d_dst, long n_images, void* cuda_stream);
+int b2c_convolve_batch_device_c64(b2c_plan* plan, const double* d_src, const double* d_kernel, int kernel_is_shared,
+                                  double* d_dst, long n_images, void* cuda_stream);
+
 /* No counterpart in the reference.  Batched shared-kernel convolution with DEVICE buffers that
  * calls no cudaMalloc / cudaFree / allocating routine at all -- for callers that cannot allocate
  * GPU memory when they convolve: plug-ins inside an application whose memory pool already owns the
