@@ -15,7 +15,7 @@ plan = b2c.Plan(b2c.LINEAR_SAME, 100, 100, 15, 15)
 for _ in range(2):
     plan.convolve_batch_device(src.data_ptr(), ker.data_ptr(), 1, dst.data_ptr(), n, 0)
 torch.cuda.synchronize()
-G = 296
+G = int(os.environ.get("B2C_TRACE_CTAS", "296"))
 N = G * 8 * 16
 buf = (ctypes.c_longlong * N)()
 L = b2c.lib()
