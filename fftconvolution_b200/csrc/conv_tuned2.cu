@@ -16,9 +16,6 @@
 // frequency p + R1*s.  The Hermitian partner of pos is P + R2 - 1 - pos for p >= 1 and R2 - s for
 // p == 0; frequencies 0 and P/2 are their own partners and park their second half in two spare
 // columns (P, P+1).
-#include <cstdlib>
-#include <cstring>
-
 #include "conv_params.h"
 
 namespace b2c {
@@ -145,10 +142,6 @@ __global__ void __launch_bounds__(512, 1) kspec_kernel(const double* __restrict_
   }
 }
 
-}  // namespace t2
-cudaError_t launch_tuned2x2_108(const t2::Params& p, int sms, cudaStream_t st);   // conv_tuned2x2.cu
-namespace t2 {
-
 template <int R1, int R2>
 cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, cudaStream_t st, int* launches) {
   typedef Geo<R1, R2> G;
@@ -159,10 +152,6 @@ cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, c
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     ++*launches;
-  }
-  if (R1 == 12 && R2 == 9 && (p.sh_h | p.sh_w) == 0) {   // experiment: two images per CTA (conv_tuned2x2.cu)
-    const char* e = getenv("B2C_P108");
-    if (e && !strcmp(e, "x2")) { ++*launches; return launch_tuned2x2_108(p, sms, st); }
   }
   int occ = 0;
   cudaFuncSetAttribute(conv_kernel<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);

@@ -485,7 +485,7 @@ def test_headline_full_size_properties(b2c, oracle, torch_cuda):
     assert float((d_dst - d_src).abs().max()) < 1e-13
 
 
-@pytest.mark.parametrize("kernel", ["t2", "pfa", "x2"])
+@pytest.mark.parametrize("kernel", ["t2", "pfa"])
 def test_tuned_108_kernel_vs_oracle_and_generic(b2c, oracle, torch_cuda, kernel, monkeypatch):
     """Plans whose periods are 108 x 108 (the headline shape) run on the (12, 9) member of conv_tuned2.cu; the
     five-pass prime-factor kernel of conv_pfa108.cu is the alternative behind B2C_P108=pfa.  Both against the
