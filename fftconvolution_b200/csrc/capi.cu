@@ -30,6 +30,9 @@ int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int group = 1);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
 int occupancy_direct(int hk, int hd, bool wrap, size_t smem);
+bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
+                          int* pitch, int* col_shift, size_t* smem);
+int occupancy_direct_bulk(int hk, size_t smem);
 // conv_big2d.cu
 cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_t st, int* launches);
@@ -615,9 +618,18 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
     while (g > 1 && direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw, (int)g) > 56 * 1024) --g;
     q.group = (int)std::max<long>(1, g);
   }
-  const size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw, q.group);
+  size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw, q.group);
   q.sp_w = spw;
-  int occ = occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
+  // whole images, no wrapping, aligned rows: the bulk-staged variant (source rows copied by the TMA engine)
+  static const bool no_bulk = getenv("B2C_DIRECT_NO_BULK") != nullptr;   // A/B measurements
+  int bpitch = 0, bshift = 0;
+  size_t bsmem = 0;
+  if (!no_bulk && q.wrap_h == 0 && q.wrap_w == 0 && (reinterpret_cast<size_t>(d_src) & 15) == 0 &&
+      direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, q.tile_h, q.group, &bpitch, &bshift, &bsmem) &&
+      bsmem <= budget1 && occupancy_direct_bulk(q.hk, bsmem) >= 1) {
+    q.bulk = 1; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
+  }
+  int occ = q.bulk ? occupancy_direct_bulk(q.hk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);

@@ -10,6 +10,7 @@
 // is a template parameter so that the window lives in registers.  Kernels taller than
 // kMaxDirectHK use the general variant (one load per FMA), which only matters for forced-path
 // tests: the planner never picks the direct path there.
+#include "bulk_copy.cuh"
 #include "conv_params.h"
 
 namespace b2c {
@@ -171,6 +172,135 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
   }
 }
 
+// ---- bulk-staged variant ---------------------------------------------------------------------------------------
+// Whole images with a compile-time kernel height, no wrapping: the staging loop of direct_kernel (one 8-byte load,
+// ~15 instructions of index arithmetic and bounds tests per source element: ncu showed 90 instructions per OUTPUT
+// pixel at 100 x 100 (*) 3 x 3, issue slots 55 % busy, HBM 41 %) is replaced by one bulk asynchronous copy per source
+// row (cp.async.bulk + mbarrier, issued by as many threads as there are rows): no registers, no index arithmetic, the
+// zero halo is written once per CTA and never touched again because the copies only land in the interior.
+// Layout of the staged tile: row u <-> source row sr0 + u, column v <-> source column sc0 + v - col_shift
+// (sr0 = off_h - (hk-1), sc0 = off_w - (wk-1); col_shift in {0, 1} makes every copy's destination 16-byte aligned).
+// Work units as in direct_kernel: a row tile of one image, or `group` whole small images.  With row tiles the rows
+// above / below the source are cleared per unit (they move with the tile).
+// The host selects this variant only when every copy is 16-byte aligned at both ends (direct_bulk_geometry).
+template <int HK>
+__global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __grid_constant__ DirectParams p) {
+  constexpr int TI = 8;
+  unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2c_smem_direct);
+  double* kflip = reinterpret_cast<double*>(b2c_smem_direct + 16);   // [wk][hk_pad]: column-major, flipped
+  constexpr int hk = HK, hk_pad = (HK + 1) & ~1;
+  double* S = kflip + (size_t)p.wk * hk_pad;
+  const int pitch = p.sp_w;
+  const size_t src_sz = (size_t)p.hs * p.ws, ker_sz = (size_t)p.hk * p.wk, dst_sz = (size_t)p.hd * p.wd;
+  const int group = p.group;
+  const long units = group > 1 ? (p.n_images + group - 1) / group : p.n_images * p.tiles_per_image;
+  const int rows_max = p.tile_h + hk - 1, nelem = rows_max * pitch;   // staged rows / doubles per image slot
+  const int sc0 = p.off_w - (p.wk - 1);
+  const int c_lo = max(0, sc0), c_hi = min(p.ws, sc0 + p.wd + p.wk - 1);   // copied columns of the source
+  const unsigned row_bytes = (unsigned)(c_hi - c_lo) * 8u;
+  const int v_lo = c_lo - sc0 + p.col_shift;                                // their first staged column
+  for (int i = threadIdx.x; i < group * nelem; i += kDirectThreads) S[i] = 0.0;   // halo (and interior, once)
+  bulk::fence_async_proxy();   // writers fence, then the barrier at the top of the loop, then the copy engine may write
+  if (threadIdx.x == 0) {
+    bulk::mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  unsigned phase = 0;
+  bool kernel_loaded = false;
+  for (long work = blockIdx.x; work < units; work += gridDim.x) {
+    const long img0 = group > 1 ? work * group : work / p.tiles_per_image;
+    const int ng = group > 1 ? (int)min((long)group, p.n_images - img0) : 1;
+    const int tile = group > 1 ? 0 : (int)(work - img0 * p.tiles_per_image);
+    const int i0 = tile * p.tile_h;
+    const int th = min(p.tile_h, p.hd - i0);
+    const int rows = th + hk - 1;
+    const int sr0 = i0 + p.off_h - (hk - 1);
+    const int r_lo = max(0, sr0), r_hi = min(p.hs, sr0 + rows);   // copied rows of the source
+    const int nr = max(0, r_hi - r_lo);
+    __syncthreads();   // previous unit's readers are done with S and kflip
+    if (p.tiles_per_image > 1) {
+      // row tiles: the rows above / below the source change from tile to tile and may hold an earlier tile's data
+      const int top = r_lo - sr0, bot = r_hi - sr0;   // staged rows [top, bot) are copied
+      for (int i = threadIdx.x; i < (top + rows - bot) * pitch; i += kDirectThreads) {
+        const int u = i / pitch, v = i - u * pitch;
+        S[(u < top ? u : bot + (u - top)) * pitch + v] = 0.0;
+      }
+    }
+    bulk::fence_async_proxy();   // this unit's zeros are fenced before the next unit's barrier (its copies may overwrite them)
+    // (copies may complete before the byte count is posted: the phase cannot end before thread 0 has arrived)
+    if (threadIdx.x == 0) bulk::mbar_expect_tx(bar, row_bytes * (unsigned)(nr * ng));
+    const double* a = p.src + (size_t)img0 * src_sz;
+    for (int i = threadIdx.x; i < nr * ng; i += kDirectThreads) {
+      const int g = i / nr, r = r_lo + (i - g * nr);
+      bulk::bulk_g2s(S + g * nelem + (r - sr0) * pitch + v_lo, a + (size_t)g * src_sz + (size_t)r * p.ws + c_lo, row_bytes, bar);
+    }
+    const bool load_kernel = !(p.kernel_is_shared && kernel_loaded);
+    if (load_kernel) {
+      const double* k = p.ker + (p.kernel_is_shared ? 0 : (size_t)img0 * ker_sz);
+      for (int idx = threadIdx.x; idx < p.wk * hk_pad; idx += kDirectThreads) {
+        const int c = idx / hk_pad, r = idx - c * hk_pad;
+        kflip[idx] = r < hk ? __ldg(&k[(size_t)(hk - 1 - r) * p.wk + (p.wk - 1 - c)]) : 0.0;
+      }
+      kernel_loaded = true;
+    }
+    bulk::mbar_wait(bar, phase);   // (completes at once when the unit has no source rows)
+    phase ^= 1u;
+    if (load_kernel) __syncthreads();   // kflip was written by other threads
+    double* d = p.dst + (size_t)img0 * dst_sz;
+    const int blocks = (th + TI - 1) / TI;
+    const int per_image = blocks * p.wd;
+    const float inv_per_image = 1.0f / (float)per_image, inv_wd = 1.0f / (float)p.wd;
+    for (int task = threadIdx.x; task < ng * per_image; task += kDirectThreads) {
+      const int g = group > 1 ? fast_div(task, per_image, inv_per_image) : 0;
+      const int t2 = task - g * per_image;
+      const int b = fast_div(t2, p.wd, inv_wd), j = t2 - b * p.wd;   // adjacent lanes -> adjacent columns
+      const int r0 = b * TI;
+      double acc[TI];
+#pragma unroll
+      for (int t = 0; t < TI; ++t) acc[t] = 0.0;
+      const double* col = S + (g * nelem + r0 * pitch + j + p.col_shift);
+      const int last = rows - 1 - r0;   // highest staged row of this window
+      for (int kc = 0; kc < p.wk; ++kc) {
+        double w[TI + HK - 1];
+#pragma unroll
+        for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[min(u, last) * pitch + kc];
+        const double* kv = kflip + kc * hk_pad;
+#pragma unroll
+        for (int kr = 0; kr < HK; ++kr) {
+          const double kk = kv[kr];
+#pragma unroll
+          for (int t = 0; t < TI; ++t) acc[t] = fma(kk, w[t + kr], acc[t]);
+        }
+      }
+      double* o = d + (size_t)g * dst_sz + (size_t)(i0 + r0) * p.wd + j;
+#pragma unroll
+      for (int t = 0; t < TI; ++t)
+        if (r0 + t < th) o[(size_t)t * p.wd] = acc[t];
+    }
+  }
+}
+
+// Can the bulk-staged variant run this geometry?  Fills the staged pitch, the column shift and the bytes of shared
+// memory.  Conditions: every row copy starts and ends on a 16-byte boundary in global AND shared memory.
+bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
+                          int* pitch, int* col_shift, size_t* smem) {
+  if (hk < 1 || hk > kMaxDirectHK || hd < 8 || (ws & 1)) return false;
+  if (group > 1 && (((size_t)hs * ws) & 1)) return false;     // every image of a group starts 16-byte aligned
+  const int sc0 = off_w - (wk - 1), cols = wd + wk - 1;
+  const int c_lo = sc0 > 0 ? sc0 : 0, c_hi = ws < sc0 + cols ? ws : sc0 + cols;
+  const int rows = tile_h + hk - 1;
+  if (c_hi <= c_lo) return false;
+  if ((c_lo & 1) || ((c_hi - c_lo) & 1)) return false;        // source side: ws is even, so rows start aligned
+  const int shift = (c_lo - sc0) & 1;                          // destination side: staged column c_lo - sc0 + shift is even
+  const int hk_pad = (hk + 1) & ~1;
+  if ((wk * hk_pad) & 1) return false;                         // S itself starts 16-byte aligned behind kflip
+  int pt = cols + shift;
+  pt = (pt + 1) & ~1;
+  *pitch = pt; *col_shift = shift;
+  *smem = 16 + sizeof(double) * ((size_t)wk * hk_pad + (size_t)group * rows * pt);
+  return true;
+}
+
 // Shared memory the direct kernel needs for a given row tile; the staged row pitch is returned
 // through *sp_w_out.
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int group) {
@@ -200,7 +330,32 @@ static direct_fn direct_variant(int hk, int hd, bool wrap) {
   return pick<0>(tall, wrap);
 }
 
+static direct_fn direct_bulk_variant(int hk) {
+  switch (hk) {
+    case 1: return direct_bulk_kernel<1>;   case 2: return direct_bulk_kernel<2>;   case 3: return direct_bulk_kernel<3>;   case 4: return direct_bulk_kernel<4>;
+    case 5: return direct_bulk_kernel<5>;   case 6: return direct_bulk_kernel<6>;   case 7: return direct_bulk_kernel<7>;   case 8: return direct_bulk_kernel<8>;
+    case 9: return direct_bulk_kernel<9>;   case 10: return direct_bulk_kernel<10>; case 11: return direct_bulk_kernel<11>; case 12: return direct_bulk_kernel<12>;
+    case 13: return direct_bulk_kernel<13>; case 14: return direct_bulk_kernel<14>; case 15: return direct_bulk_kernel<15>; case 16: return direct_bulk_kernel<16>;
+  }
+  return nullptr;
+}
+
+int occupancy_direct_bulk(int hk, size_t smem) {
+  int n = 0;
+  direct_fn fn = direct_bulk_variant(hk);
+  if (!fn) return 0;
+  cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
+  return n;
+}
+
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
+  if (p.bulk) {
+    direct_fn fn = direct_bulk_variant(p.hk);
+    cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    fn<<<grid, kDirectThreads, smem, st>>>(p);
+    return cudaGetLastError();
+  }
   direct_fn fn = direct_variant(p.hk, p.hd, p.wrap_h > 0);
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   fn<<<grid, kDirectThreads, smem, st>>>(p);
