@@ -31,8 +31,8 @@ size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
 int occupancy_direct(int hk, int hd, bool wrap, size_t smem);
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
-                          int* pitch, int* col_shift, size_t* smem);
-int occupancy_direct_bulk(int hk, size_t smem);
+                          int nbuf, int* pitch, int* col_shift, size_t* smem);
+int occupancy_direct_bulk(int hk, int nbuf, size_t smem);
 // conv_big2d.cu
 cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_t st, int* launches);
@@ -622,14 +622,21 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   q.sp_w = spw;
   // whole images, no wrapping, aligned rows: the bulk-staged variant (source rows copied by the TMA engine)
   static const bool no_bulk = getenv("B2C_DIRECT_NO_BULK") != nullptr;   // A/B measurements
-  int bpitch = 0, bshift = 0;
-  size_t bsmem = 0;
-  if (!no_bulk && q.wrap_h == 0 && q.wrap_w == 0 && (reinterpret_cast<size_t>(d_src) & 15) == 0 &&
-      direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, q.tile_h, q.group, &bpitch, &bshift, &bsmem) &&
-      bsmem <= budget1 && occupancy_direct_bulk(q.hk, bsmem) >= 1) {
-    q.bulk = 1; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
+  static const int force_nbuf = getenv("B2C_DIRECT_NBUF") ? atoi(getenv("B2C_DIRECT_NBUF")) : 0;
+  if (!no_bulk && q.wrap_h == 0 && q.wrap_w == 0 && (reinterpret_cast<size_t>(d_src) & 15) == 0) {
+    // two tile buffers per CTA (the next unit's copies fly during this unit's arithmetic) when two such CTAs still
+    // fit an SM, else one buffer and two CTAs
+    for (int nbuf = 2; nbuf >= 1 && !q.bulk; --nbuf) {
+      if (force_nbuf && nbuf != force_nbuf) continue;
+      int bpitch = 0, bshift = 0;
+      size_t bsmem = 0;
+      if (direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, q.tile_h, q.group, nbuf, &bpitch, &bshift, &bsmem) &&
+          bsmem <= (nbuf == 2 && !force_nbuf ? budget2 : budget1) && occupancy_direct_bulk(q.hk, nbuf, bsmem) >= 1) {
+        q.bulk = nbuf; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
+      }
+    }
   }
-  int occ = q.bulk ? occupancy_direct_bulk(q.hk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
+  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.bulk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);

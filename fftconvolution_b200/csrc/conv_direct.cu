@@ -183,41 +183,43 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
 // Work units as in direct_kernel: a row tile of one image, or `group` whole small images.  With row tiles the rows
 // above / below the source are cleared per unit (they move with the tile).
 // The host selects this variant only when every copy is 16-byte aligned at both ends (direct_bulk_geometry).
-template <int HK>
+// NBUF = 2: two staged tiles per CTA -- the copies of the next work unit are in flight while this one is computed.
+template <int HK, int NBUF>
 __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __grid_constant__ DirectParams p) {
   constexpr int TI = 8;
-  unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2c_smem_direct);
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(b2c_smem_direct);   // [2]
   double* kflip = reinterpret_cast<double*>(b2c_smem_direct + 16);   // [wk][hk_pad]: column-major, flipped
   constexpr int hk = HK, hk_pad = (HK + 1) & ~1;
-  double* S = kflip + (size_t)p.wk * hk_pad;
+  double* S0 = kflip + (size_t)p.wk * hk_pad;
   const int pitch = p.sp_w;
   const size_t src_sz = (size_t)p.hs * p.ws, ker_sz = (size_t)p.hk * p.wk, dst_sz = (size_t)p.hd * p.wd;
   const int group = p.group;
   const long units = group > 1 ? (p.n_images + group - 1) / group : p.n_images * p.tiles_per_image;
   const int rows_max = p.tile_h + hk - 1, nelem = rows_max * pitch;   // staged rows / doubles per image slot
+  const int bufsz = group * nelem;
   const int sc0 = p.off_w - (p.wk - 1);
   const int c_lo = max(0, sc0), c_hi = min(p.ws, sc0 + p.wd + p.wk - 1);   // copied columns of the source
   const unsigned row_bytes = (unsigned)(c_hi - c_lo) * 8u;
   const int v_lo = c_lo - sc0 + p.col_shift;                                // their first staged column
-  for (int i = threadIdx.x; i < group * nelem; i += kDirectThreads) S[i] = 0.0;   // halo (and interior, once)
-  bulk::fence_async_proxy();   // writers fence, then the barrier at the top of the loop, then the copy engine may write
+  for (int i = threadIdx.x; i < NBUF * bufsz; i += kDirectThreads) S0[i] = 0.0;   // halo (and interior, once)
+  bulk::fence_async_proxy();   // writers fence, then a barrier, then the copy engine may write
   if (threadIdx.x == 0) {
-    bulk::mbar_init(bar, 1);
+    bulk::mbar_init(&bars[0], 1);
+    bulk::mbar_init(&bars[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  unsigned phase = 0;
-  bool kernel_loaded = false;
-  for (long work = blockIdx.x; work < units; work += gridDim.x) {
+  __syncthreads();
+
+  // geometry of a work unit and the copies that stage it into buffer `buf` (all threads call this together)
+  auto stage = [&](long work, int buf) {
     const long img0 = group > 1 ? work * group : work / p.tiles_per_image;
     const int ng = group > 1 ? (int)min((long)group, p.n_images - img0) : 1;
-    const int tile = group > 1 ? 0 : (int)(work - img0 * p.tiles_per_image);
-    const int i0 = tile * p.tile_h;
-    const int th = min(p.tile_h, p.hd - i0);
-    const int rows = th + hk - 1;
+    const int i0 = group > 1 ? 0 : (int)(work - img0 * p.tiles_per_image) * p.tile_h;
+    const int rows = min(p.tile_h, p.hd - i0) + hk - 1;
     const int sr0 = i0 + p.off_h - (hk - 1);
     const int r_lo = max(0, sr0), r_hi = min(p.hs, sr0 + rows);   // copied rows of the source
     const int nr = max(0, r_hi - r_lo);
-    __syncthreads();   // previous unit's readers are done with S and kflip
+    double* S = S0 + buf * bufsz;
     if (p.tiles_per_image > 1) {
       // row tiles: the rows above / below the source change from tile to tile and may hold an earlier tile's data
       const int top = r_lo - sr0, bot = r_hi - sr0;   // staged rows [top, bot) are copied
@@ -225,14 +227,33 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
         const int u = i / pitch, v = i - u * pitch;
         S[(u < top ? u : bot + (u - top)) * pitch + v] = 0.0;
       }
+      bulk::fence_async_proxy();   // fenced before the barrier that precedes the next copies into this buffer
     }
-    bulk::fence_async_proxy();   // this unit's zeros are fenced before the next unit's barrier (its copies may overwrite them)
     // (copies may complete before the byte count is posted: the phase cannot end before thread 0 has arrived)
-    if (threadIdx.x == 0) bulk::mbar_expect_tx(bar, row_bytes * (unsigned)(nr * ng));
+    if (threadIdx.x == 0) bulk::mbar_expect_tx(&bars[buf], row_bytes * (unsigned)(nr * ng));
     const double* a = p.src + (size_t)img0 * src_sz;
     for (int i = threadIdx.x; i < nr * ng; i += kDirectThreads) {
       const int g = i / nr, r = r_lo + (i - g * nr);
-      bulk::bulk_g2s(S + g * nelem + (r - sr0) * pitch + v_lo, a + (size_t)g * src_sz + (size_t)r * p.ws + c_lo, row_bytes, bar);
+      bulk::bulk_g2s(S + g * nelem + (r - sr0) * pitch + v_lo, a + (size_t)g * src_sz + (size_t)r * p.ws + c_lo, row_bytes, &bars[buf]);
+    }
+  };
+
+  unsigned phase0 = 0u, phase1 = 0u;
+  bool kernel_loaded = false;
+  long it = 0;
+  if (NBUF == 2 && (long)blockIdx.x < units) stage(blockIdx.x, 0);
+  for (long work = blockIdx.x; work < units; work += gridDim.x, ++it) {
+    const int buf = NBUF == 2 ? (int)(it & 1) : 0;
+    const long img0 = group > 1 ? work * group : work / p.tiles_per_image;
+    const int ng = group > 1 ? (int)min((long)group, p.n_images - img0) : 1;
+    const int i0 = group > 1 ? 0 : (int)(work - img0 * p.tiles_per_image) * p.tile_h;
+    const int th = min(p.tile_h, p.hd - i0);
+    const int rows = th + hk - 1;
+    __syncthreads();   // the previous unit's readers are done with the other buffer (NBUF 2) / this buffer (NBUF 1) and kflip
+    if (NBUF == 2) {
+      if (work + gridDim.x < units) stage(work + gridDim.x, buf ^ 1);
+    } else {
+      stage(work, 0);
     }
     const bool load_kernel = !(p.kernel_is_shared && kernel_loaded);
     if (load_kernel) {
@@ -243,9 +264,10 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
       }
       kernel_loaded = true;
     }
-    bulk::mbar_wait(bar, phase);   // (completes at once when the unit has no source rows)
-    phase ^= 1u;
+    bulk::mbar_wait(&bars[buf], buf ? phase1 : phase0);   // (completes at once when the unit has no source rows)
+    if (buf) phase1 ^= 1u; else phase0 ^= 1u;
     if (load_kernel) __syncthreads();   // kflip was written by other threads
+    const double* S = S0 + buf * bufsz;
     double* d = p.dst + (size_t)img0 * dst_sz;
     const int blocks = (th + TI - 1) / TI;
     const int per_image = blocks * p.wd;
@@ -283,7 +305,7 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
 // Can the bulk-staged variant run this geometry?  Fills the staged pitch, the column shift and the bytes of shared
 // memory.  Conditions: every row copy starts and ends on a 16-byte boundary in global AND shared memory.
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
-                          int* pitch, int* col_shift, size_t* smem) {
+                          int nbuf, int* pitch, int* col_shift, size_t* smem) {
   if (hk < 1 || hk > kMaxDirectHK || hd < 8 || (ws & 1)) return false;
   if (group > 1 && (((size_t)hs * ws) & 1)) return false;     // every image of a group starts 16-byte aligned
   const int sc0 = off_w - (wk - 1), cols = wd + wk - 1;
@@ -297,7 +319,7 @@ bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int of
   int pt = cols + shift;
   pt = (pt + 1) & ~1;
   *pitch = pt; *col_shift = shift;
-  *smem = 16 + sizeof(double) * ((size_t)wk * hk_pad + (size_t)group * rows * pt);
+  *smem = 16 + sizeof(double) * ((size_t)wk * hk_pad + (size_t)nbuf * group * rows * pt);
   return true;
 }
 
@@ -330,19 +352,23 @@ static direct_fn direct_variant(int hk, int hd, bool wrap) {
   return pick<0>(tall, wrap);
 }
 
-static direct_fn direct_bulk_variant(int hk) {
+template <int NBUF>
+static direct_fn direct_bulk_pick(int hk) {
   switch (hk) {
-    case 1: return direct_bulk_kernel<1>;   case 2: return direct_bulk_kernel<2>;   case 3: return direct_bulk_kernel<3>;   case 4: return direct_bulk_kernel<4>;
-    case 5: return direct_bulk_kernel<5>;   case 6: return direct_bulk_kernel<6>;   case 7: return direct_bulk_kernel<7>;   case 8: return direct_bulk_kernel<8>;
-    case 9: return direct_bulk_kernel<9>;   case 10: return direct_bulk_kernel<10>; case 11: return direct_bulk_kernel<11>; case 12: return direct_bulk_kernel<12>;
-    case 13: return direct_bulk_kernel<13>; case 14: return direct_bulk_kernel<14>; case 15: return direct_bulk_kernel<15>; case 16: return direct_bulk_kernel<16>;
+    case 1: return direct_bulk_kernel<1, NBUF>;   case 2: return direct_bulk_kernel<2, NBUF>;   case 3: return direct_bulk_kernel<3, NBUF>;
+    case 4: return direct_bulk_kernel<4, NBUF>;   case 5: return direct_bulk_kernel<5, NBUF>;   case 6: return direct_bulk_kernel<6, NBUF>;
+    case 7: return direct_bulk_kernel<7, NBUF>;   case 8: return direct_bulk_kernel<8, NBUF>;   case 9: return direct_bulk_kernel<9, NBUF>;
+    case 10: return direct_bulk_kernel<10, NBUF>; case 11: return direct_bulk_kernel<11, NBUF>; case 12: return direct_bulk_kernel<12, NBUF>;
+    case 13: return direct_bulk_kernel<13, NBUF>; case 14: return direct_bulk_kernel<14, NBUF>; case 15: return direct_bulk_kernel<15, NBUF>;
+    case 16: return direct_bulk_kernel<16, NBUF>;
   }
   return nullptr;
 }
+static direct_fn direct_bulk_variant(int hk, int nbuf) { return nbuf == 2 ? direct_bulk_pick<2>(hk) : direct_bulk_pick<1>(hk); }
 
-int occupancy_direct_bulk(int hk, size_t smem) {
+int occupancy_direct_bulk(int hk, int nbuf, size_t smem) {
   int n = 0;
-  direct_fn fn = direct_bulk_variant(hk);
+  direct_fn fn = direct_bulk_variant(hk, nbuf);
   if (!fn) return 0;
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
@@ -351,7 +377,7 @@ int occupancy_direct_bulk(int hk, size_t smem) {
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
   if (p.bulk) {
-    direct_fn fn = direct_bulk_variant(p.hk);
+    direct_fn fn = direct_bulk_variant(p.hk, p.bulk);
     cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     fn<<<grid, kDirectThreads, smem, st>>>(p);
     return cudaGetLastError();

@@ -35,7 +35,7 @@ struct DirectParams {
   int sp_w;              // padded staged-source row length (doubles)
   int kernel_is_shared;
   // bulk-staged variant (conv_direct.cu: direct_bulk_kernel): whole images, rows copied by the TMA engine
-  int bulk;              // 1: eligible and selected by the host
+  int bulk;              // 0: element-wise staging; 1 / 2: bulk-staged with that many tile buffers per CTA
   int col_shift;         // staged column of source column c is c - (off_w - (wk - 1)) + col_shift (keeps copies 16-byte aligned)
   const double* src;
   const double* ker;
