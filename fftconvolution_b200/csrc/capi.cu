@@ -270,6 +270,16 @@ int auto_path(const Plan2D& pl, bool shared) {
   else t_direct = bytes / 3.4e12 + fma / 4.5e12 + (shared ? std::min(2e-9, bytes * 1.25e-13) : per_image);   // long rows: one tile per CTA
   if (pl.h.n_ker > 16) t_direct *= 4.0;
   if (pl.mode == B2C_CIRCULAR_SAME) t_direct *= 1.35;   // wrapped source indices (profiles/r02_crossover_all_modes.csv)
+  {
+    // bulk-staged variant (whole rows copied by the TMA engine, conv_direct.cu): streams at 6.4 TB/s plus 10.4 TFMA/s
+    // (fit of profiles/r02h_direct_bulk_staging.txt); the shapes it takes are the ones direct_bulk_geometry accepts
+    int bp, bs;
+    size_t bm;
+    if (pl.mode != B2C_CIRCULAR_SAME && shared &&
+        direct_bulk_geometry(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
+                             pl.h.n_dst, 1, 1, &bp, &bs, &bm) && bm <= 227 * 1024)
+      t_direct = bytes / 6.4e12 + fma / 10.4e12 + 0.3e-9;
+  }
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
   if (shared) cost *= 0.5;  // two images per transform
