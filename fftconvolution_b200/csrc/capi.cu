@@ -32,7 +32,7 @@ cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStre
 int occupancy_direct(int hk, int hd, bool wrap, size_t smem);
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
                           int nbuf, int* pitch, int* col_shift, size_t* smem);
-int occupancy_direct_bulk(int hk, int nbuf, size_t smem);
+int occupancy_direct_bulk(int hk, int hd, int nbuf, size_t smem);
 // conv_big2d.cu
 cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_t st, int* launches);
@@ -278,7 +278,8 @@ int auto_path(const Plan2D& pl, bool shared) {
     if (pl.mode != B2C_CIRCULAR_SAME && shared &&
         direct_bulk_geometry(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
                              pl.h.n_dst, 1, 1, &bp, &bs, &bm) && bm <= 227 * 1024)
-      t_direct = bytes / 6.4e12 + fma / 10.4e12 + 0.3e-9;
+      t_direct = pl.h.n_dst >= 8 ? bytes / 6.4e12 + fma / 10.4e12 + 0.3e-9
+                                 : bytes / 5.2e12 + fma / 4.55e12 + std::min(0.9e-9, bytes * 9e-14);   // one row per thread
   }
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
@@ -293,7 +294,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
                       pl.w.fold == 0 && pl.w.kwrap == pl.w.P;
   const double t_fft = tuned    ? ((pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.5e-9) * (shared ? 1.0 : 1.35)
-                       : tuned1 ? (pl.w.P <= 512 ? 4.5e-12 * pl.w.P : 6.3e-12 * pl.w.P + 0.3e-9)
+                       : tuned1 ? (pl.w.P <= 512 ? 5.3e-12 * pl.w.P - 0.14e-9 : 6.3e-12 * pl.w.P + 0.3e-9)
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
   int spw;
@@ -641,12 +642,12 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
       int bpitch = 0, bshift = 0;
       size_t bsmem = 0;
       if (direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, q.tile_h, q.group, nbuf, &bpitch, &bshift, &bsmem) &&
-          bsmem <= (nbuf == 2 && !force_nbuf ? budget2 : budget1) && occupancy_direct_bulk(q.hk, nbuf, bsmem) >= 1) {
+          bsmem <= (nbuf == 2 && !force_nbuf ? budget2 : budget1) && occupancy_direct_bulk(q.hk, q.hd, nbuf, bsmem) >= 1) {
         q.bulk = nbuf; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
       }
     }
   }
-  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.bulk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
+  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.hd, q.bulk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);

@@ -184,9 +184,8 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
 // above / below the source are cleared per unit (they move with the tile).
 // The host selects this variant only when every copy is 16-byte aligned at both ends (direct_bulk_geometry).
 // NBUF = 2: two staged tiles per CTA -- the copies of the next work unit are in flight while this one is computed.
-template <int HK, int NBUF>
+template <int HK, int NBUF, int TI>
 __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __grid_constant__ DirectParams p) {
-  constexpr int TI = 8;
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(b2c_smem_direct);   // [2]
   double* kflip = reinterpret_cast<double*>(b2c_smem_direct + 16);   // [wk][hk_pad]: column-major, flipped
   constexpr int hk = HK, hk_pad = (HK + 1) & ~1;
@@ -306,7 +305,7 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
 // memory.  Conditions: every row copy starts and ends on a 16-byte boundary in global AND shared memory.
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
                           int nbuf, int* pitch, int* col_shift, size_t* smem) {
-  if (hk < 1 || hk > kMaxDirectHK || hd < 8 || (ws & 1)) return false;
+  if (hk < 1 || hk > kMaxDirectHK || (ws & 1)) return false;
   if (group > 1 && (((size_t)hs * ws) & 1)) return false;     // every image of a group starts 16-byte aligned
   const int sc0 = off_w - (wk - 1), cols = wd + wk - 1;
   const int c_lo = sc0 > 0 ? sc0 : 0, c_hi = ws < sc0 + cols ? ws : sc0 + cols;
@@ -352,23 +351,27 @@ static direct_fn direct_variant(int hk, int hd, bool wrap) {
   return pick<0>(tall, wrap);
 }
 
-template <int NBUF>
+template <int NBUF, int TI>
 static direct_fn direct_bulk_pick(int hk) {
   switch (hk) {
-    case 1: return direct_bulk_kernel<1, NBUF>;   case 2: return direct_bulk_kernel<2, NBUF>;   case 3: return direct_bulk_kernel<3, NBUF>;
-    case 4: return direct_bulk_kernel<4, NBUF>;   case 5: return direct_bulk_kernel<5, NBUF>;   case 6: return direct_bulk_kernel<6, NBUF>;
-    case 7: return direct_bulk_kernel<7, NBUF>;   case 8: return direct_bulk_kernel<8, NBUF>;   case 9: return direct_bulk_kernel<9, NBUF>;
-    case 10: return direct_bulk_kernel<10, NBUF>; case 11: return direct_bulk_kernel<11, NBUF>; case 12: return direct_bulk_kernel<12, NBUF>;
-    case 13: return direct_bulk_kernel<13, NBUF>; case 14: return direct_bulk_kernel<14, NBUF>; case 15: return direct_bulk_kernel<15, NBUF>;
-    case 16: return direct_bulk_kernel<16, NBUF>;
+    case 1: return direct_bulk_kernel<1, NBUF, TI>;   case 2: return direct_bulk_kernel<2, NBUF, TI>;   case 3: return direct_bulk_kernel<3, NBUF, TI>;
+    case 4: return direct_bulk_kernel<4, NBUF, TI>;   case 5: return direct_bulk_kernel<5, NBUF, TI>;   case 6: return direct_bulk_kernel<6, NBUF, TI>;
+    case 7: return direct_bulk_kernel<7, NBUF, TI>;   case 8: return direct_bulk_kernel<8, NBUF, TI>;   case 9: return direct_bulk_kernel<9, NBUF, TI>;
+    case 10: return direct_bulk_kernel<10, NBUF, TI>; case 11: return direct_bulk_kernel<11, NBUF, TI>; case 12: return direct_bulk_kernel<12, NBUF, TI>;
+    case 13: return direct_bulk_kernel<13, NBUF, TI>; case 14: return direct_bulk_kernel<14, NBUF, TI>; case 15: return direct_bulk_kernel<15, NBUF, TI>;
+    case 16: return direct_bulk_kernel<16, NBUF, TI>;
   }
   return nullptr;
 }
-static direct_fn direct_bulk_variant(int hk, int nbuf) { return nbuf == 2 ? direct_bulk_pick<2>(hk) : direct_bulk_pick<1>(hk); }
+// tall: 8 output rows per thread; else (1-D rows, images shorter than 8 rows) one
+static direct_fn direct_bulk_variant(int hk, int nbuf, bool tall) {
+  if (tall) return nbuf == 2 ? direct_bulk_pick<2, 8>(hk) : direct_bulk_pick<1, 8>(hk);
+  return nbuf == 2 ? direct_bulk_pick<2, 1>(hk) : direct_bulk_pick<1, 1>(hk);
+}
 
-int occupancy_direct_bulk(int hk, int nbuf, size_t smem) {
+int occupancy_direct_bulk(int hk, int hd, int nbuf, size_t smem) {
   int n = 0;
-  direct_fn fn = direct_bulk_variant(hk, nbuf);
+  direct_fn fn = direct_bulk_variant(hk, nbuf, hd >= 8);
   if (!fn) return 0;
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
@@ -377,7 +380,7 @@ int occupancy_direct_bulk(int hk, int nbuf, size_t smem) {
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
   if (p.bulk) {
-    direct_fn fn = direct_bulk_variant(p.hk, p.bulk);
+    direct_fn fn = direct_bulk_variant(p.hk, p.bulk, p.hd >= 8);
     cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     fn<<<grid, kDirectThreads, smem, st>>>(p);
     return cudaGetLastError();

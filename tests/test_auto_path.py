@@ -29,3 +29,24 @@ def test_auto_path_within_15_percent_of_the_measured_best(b2c):
             worst = (loss, (b2c.MODE_NAMES[mode], s, k, path))
     assert modes == set(range(8))
     assert worst[0] <= 0.15, worst
+
+
+def test_auto_path_on_the_1d_table(b2c):
+    """Same bound on 1 x N rows (profiles/r02_crossover_1d.csv, tools/crossover_1d.py: N = 64 .. 4096, 3 .. 63 taps,
+    LINEAR_SAME and LINEAR_FULL), where the bulk-staged one-row direct variant meets the tuned 1-D FFT kernels."""
+    table = os.path.join(ROOT, "profiles", "r02_crossover_1d.csv")
+    rows = [r for r in csv.reader(open(table)) if r and not r[0].startswith("#")][1:]
+    assert len(rows) >= 60
+    worst = (0.0, None)
+    for r in rows:
+        mode, ns, nk = int(r[0]), int(r[1]), int(r[2])
+        fft, direct = float(r[3]), float(r[4])
+        p = b2c.Plan(mode, 1, ns, 1, nk)
+        path = p.info()["path"]
+        p.destroy()
+        chosen = fft if path == b2c.PATH_FFT else direct
+        assert chosen > 0, (mode, ns, nk)
+        loss = max(fft, direct) / chosen - 1.0
+        if loss > worst[0]:
+            worst = (loss, (b2c.MODE_NAMES[mode], ns, nk, path))
+    assert worst[0] <= 0.15, worst
