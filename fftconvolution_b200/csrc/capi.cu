@@ -294,7 +294,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   const bool tuned1 = shared && pl.h.P == 1 && pl.h.n_src == 1 && pl.h.n_ker == 1 && tuned1d_has(pl.w.P) &&
                       pl.w.fold == 0 && pl.w.kwrap == pl.w.P;
   const double t_fft = tuned    ? ((pl.h.P <= 80 ? 5.6e-12 : 6.5e-12) * pp * (pl.h.P > 118 ? 1.25 : 1.0) + 1.5e-9) * (shared ? 1.0 : 1.35)
-                       : tuned1 ? (pl.w.P <= 512 ? 5.3e-12 * pl.w.P - 0.14e-9 : 6.3e-12 * pl.w.P + 0.3e-9)
+                       : tuned1 ? (pl.w.P <= 128 ? 4.2e-12 * pl.w.P : pl.w.P <= 512 ? 5.3e-12 * pl.w.P : 6.3e-12 * pl.w.P + 0.3e-9)
                                 : std::max(10e-9, cost * (pl.h.P == 1 ? 0.25e-12 : 0.15e-12));   // 1-D transforms: fewer lines per warp
   // the direct kernel must also fit its tile in shared memory
   int spw;
