@@ -510,6 +510,10 @@ def run_b2c_arm(args):
              b2c.CIRCULAR_FULL, 100, 100, 100, 100, N3, False, SEED3, 5, 8 * (2 * 100 * 100 + 199 * 199)),
             ("configs[1] shape with per-image kernels: 100x100 (*) 15x15 LINEAR_SAME, %d per GPU" % (2 * N3),
              b2c.LINEAR_SAME, 100, 100, 15, 15, 2 * N3, False, SEED3, 10, 8 * (2 * 100 * 100 + 15 * 15)),
+            ("configs[4] small-kernel point: 100x100 (*) 3x3 LINEAR_SAME, shared kernel (direct kernel), %d per GPU" % (2 * N3),
+             b2c.LINEAR_SAME, 100, 100, 3, 3, 2 * N3, True, SEED3, 20, 8 * (2 * 100 * 100)),
+            ("configs[3] short-kernel point: 1x4096 (*) 1x3 LINEAR_SAME rows (direct kernel), %d per GPU" % (4 * N4),
+             b2c.LINEAR_SAME, 1, 4096, 1, 3, 4 * N4, True, SEED4, 20, 8 * (4096 + 4096)),
             ("configs[3]: 1x4096 (*) 1x255 LINEAR_SAME rows, shared kernel, %d per GPU" % N4,
              b2c.LINEAR_SAME, 1, 4096, 1, 255, N4, True, SEED4, 20, 8 * (4096 + 4096)),
             ("configs[3]: 4096x1 (*) 255x1 LINEAR_SAME columns, shared kernel, %d per GPU" % N4,

@@ -10,7 +10,7 @@ timeout 300 python tools/quick_bench.py 65536 20 > $O/ab.txt 2>&1
 B2C_P108=pfa timeout 300 python tools/quick_bench.py 65536 20 >> $O/ab.txt 2>&1
 cat $O/ab.txt
 [ $rc -eq 0 ] || { echo "tests failed: no profiling"; exit 1; }
-B2C_P108=pfa timeout 300 python tools/trace_pfa108.py > $O/trace_pfa108.csv 2>&1; cat $O/trace_pfa108.csv
+true
 timeout 600 python bench.py --steps 20 --warmup 3 > $O/bench.json 2> $O/bench.err; cat $O/bench.json
 CMD="timeout 300 python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-secondary"
 $CMD > $O/plain.log 2>&1 &&
