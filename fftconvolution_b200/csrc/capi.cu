@@ -228,6 +228,9 @@ struct b2c_plan {
   size_t d_one_bytes = 0;
   unsigned char* h_one = nullptr;
   size_t h_one_bytes = 0;
+  unsigned char* h_one_dev = nullptr;   // device-side address of h_one (zero-copy single calls)
+  const void* zc_dst_host = nullptr;    // last result buffer asked about, and what the device may use for it (or null)
+  double* zc_dst_dev = nullptr;
   bool ker_cached = false;      // h_one / d_one hold the kernel of the previous single call
   bool kspec_cached = false;    // ... and p->kspec holds its spectrum for the plan's current path
   bool kspec_reuse = false;     // transient: set around the inner call when the spectrum may be reused
@@ -973,7 +976,7 @@ int b2c_convolve_host(b2c_plan* p, const double* src, const double* kernel, doub
   }
   if (p->h_one_bytes < up(sb) + up(kb)) {
     if (p->h_one) cudaFreeHost(p->h_one);
-    p->h_one = nullptr; p->h_one_bytes = 0; p->ker_cached = false;
+    p->h_one = nullptr; p->h_one_bytes = 0; p->ker_cached = false; p->h_one_dev = nullptr;
     CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&p->h_one), up(sb) + up(kb), cudaHostAllocDefault));
     p->h_one_bytes = up(sb) + up(kb);
   }
@@ -981,11 +984,36 @@ int b2c_convolve_host(b2c_plan* p, const double* src, const double* kernel, doub
   double* ds = reinterpret_cast<double*>(base);
   double* dk = reinterpret_cast<double*>(base + up(sb));
   double* dd = reinterpret_cast<double*>(base + up(sb) + up(kb));
-  // one transfer from pinned staging: [src | kernel], or src alone when the kernel is the cached one
+  // Zero-copy form (default; B2C_ZEROCOPY=0 restores the copies): one call moves a few tens of KB, so its cost is the
+  // NUMBER of operations on the stream, not their size.  The kernels read the source (and a new kernel) straight from
+  // the page-locked staging buffer and, when the caller's result buffer is page-locked too (the drop-in header's
+  // ws.dst is), write the result straight into it: one launch + one synchronisation instead of copy, launch, copy.
+  static const bool zero_copy = [] { const char* e = getenv("B2C_ZEROCOPY"); return !(e && e[0] == '0'); }();
   const bool same_kernel = p->ker_cached && memcmp(p->h_one + up(sb), kernel, kb) == 0;
   memcpy(p->h_one, src, sb);
   if (!same_kernel) memcpy(p->h_one + up(sb), kernel, kb);
-  CUDA_TRY(cudaMemcpyAsync(ds, p->h_one, same_kernel ? sb : up(sb) + kb, cudaMemcpyHostToDevice, 0));
+  bool dst_direct = false;
+  if (zero_copy && sb + db <= (size_t)192 * 1024) {   // larger images: the copy engine moves them faster than kernel accesses over PCIe
+    if (!p->h_one_dev) {
+      void* dv = nullptr;
+      CUDA_TRY(cudaHostGetDevicePointer(&dv, p->h_one, 0));
+      p->h_one_dev = static_cast<unsigned char*>(dv);
+    }
+    if (p->zc_dst_host != dst) {   // ask once per buffer: the header passes the same ws.dst on every call
+      cudaPointerAttributes at;
+      p->zc_dst_host = dst;
+      p->zc_dst_dev = nullptr;
+      if (cudaPointerGetAttributes(&at, dst) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+        p->zc_dst_dev = static_cast<double*>(at.devicePointer);
+      cudaGetLastError();   // an unregistered pointer is not an error here
+    }
+    ds = reinterpret_cast<double*>(p->h_one_dev);
+    dk = reinterpret_cast<double*>(p->h_one_dev + up(sb));
+    if (p->zc_dst_dev) { dd = p->zc_dst_dev; dst_direct = true; }
+  } else {
+    // one transfer from pinned staging: [src | kernel], or src alone when the kernel is the cached one
+    CUDA_TRY(cudaMemcpyAsync(ds, p->h_one, same_kernel ? sb : up(sb) + kb, cudaMemcpyHostToDevice, 0));
+  }
   p->kspec_reuse = same_kernel && p->kspec_cached;
   p->single_call = true;
   const int rc = b2c_convolve_batch_device(p, ds, dk, 1, dd, 1, nullptr);
@@ -994,7 +1022,7 @@ int b2c_convolve_host(b2c_plan* p, const double* src, const double* kernel, doub
   if (rc) { p->ker_cached = false; p->kspec_cached = false; return rc; }
   p->ker_cached = true;
   p->kspec_cached = true;
-  CUDA_TRY(cudaMemcpyAsync(dst, dd, db, cudaMemcpyDeviceToHost, 0));
+  if (!dst_direct) CUDA_TRY(cudaMemcpyAsync(dst, dd, db, cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return 0;
 }
