@@ -31,8 +31,9 @@ size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
 int occupancy_direct(int hk, int hd, bool wrap, size_t smem);
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
-                          int nbuf, int* pitch, int* col_shift, size_t* smem);
-int occupancy_direct_bulk(int hk, int hd, int nbuf, size_t smem);
+                          int nbuf, int ti, int* pitch, int* col_shift, size_t* smem);
+int direct_bulk_ti(int hd, int wd, int tile_h, int group);
+int occupancy_direct_bulk(int hk, int ti, int nbuf, size_t smem);
 // conv_big2d.cu
 cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_t st, int* launches);
@@ -280,7 +281,7 @@ int auto_path(const Plan2D& pl, bool shared) {
     size_t bm;
     if (pl.mode != B2C_CIRCULAR_SAME && shared &&
         direct_bulk_geometry(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
-                             pl.h.n_dst, 1, 1, &bp, &bs, &bm) && bm <= 227 * 1024)
+                             pl.h.n_dst, 1, 1, direct_bulk_ti(pl.h.n_dst, pl.w.n_dst, pl.h.n_dst, 1), &bp, &bs, &bm) && bm <= 227 * 1024)
       t_direct = pl.h.n_dst >= 8 ? bytes / 6.4e12 + fma / 10.4e12 + 0.3e-9
                                  : bytes / 5.2e12 + fma / 4.55e12 + std::min(0.9e-9, bytes * 9e-14);   // one row per thread
   }
@@ -620,6 +621,8 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
     return fail(B2C_ESIZE, "direct kernel: %dx%d kernel does not fit in shared memory", q.hk, q.wk);
   // a batch too small to fill the SMs with whole-image tiles: shorter tiles (8 rows = one task row per thread)
   while (tile > 8 && n * ((q.hd + tile - 1) / tile) < (long)p->ctx->sms) tile = std::max(8, ((tile + 1) / 2 + 7) / 8 * 8);
+  static const int force_tile = getenv("B2C_DIRECT_TILE") ? atoi(getenv("B2C_DIRECT_TILE")) : 0;   // A/B measurements
+  if (force_tile > 0 && force_tile < tile) tile = force_tile;
   q.tile_h = tile;
   q.tiles_per_image = (q.hd + tile - 1) / tile;
   // Small images with a shared kernel: a CTA takes `group` whole images at a time, enough for about three
@@ -639,18 +642,25 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   static const int force_nbuf = getenv("B2C_DIRECT_NBUF") ? atoi(getenv("B2C_DIRECT_NBUF")) : 0;
   if (!no_bulk && q.wrap_h == 0 && q.wrap_w == 0 && (reinterpret_cast<size_t>(d_src) & 15) == 0) {
     // two tile buffers per CTA (the next unit's copies fly during this unit's arithmetic) when two such CTAs still
-    // fit an SM, else one buffer and two CTAs
-    for (int nbuf = 2; nbuf >= 1 && !q.bulk; --nbuf) {
-      if (force_nbuf && nbuf != force_nbuf) continue;
+    // fit an SM; else two buffers of half an image where the halves are whole blocks of task rows (100 x 100 (*) 7 x 7:
+    // 15.5 -> 16.4 M conv/s; ragged halves measured slower); else one buffer and two CTAs
+    struct Cand { int tile, nbuf; } cands[3] = {{q.tile_h, 2}, {0, 2}, {q.tile_h, 1}};
+    if (q.tiles_per_image == 1 && q.group == 1 && q.hd % 2 == 0 && q.hd >= 32 &&
+        (q.hd / 2) % direct_bulk_ti(q.hd, q.wd, q.hd / 2, 1) == 0 && n * 2 >= (long)p->ctx->sms * 2)
+      cands[1].tile = q.hd / 2;
+    for (const Cand& c : cands) {
+      if (q.bulk || c.tile <= 0 || (force_nbuf && c.nbuf != force_nbuf)) continue;
       int bpitch = 0, bshift = 0;
       size_t bsmem = 0;
-      if (direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, q.tile_h, q.group, nbuf, &bpitch, &bshift, &bsmem) &&
-          bsmem <= (nbuf == 2 && !force_nbuf ? budget2 : budget1) && occupancy_direct_bulk(q.hk, q.hd, nbuf, bsmem) >= 1) {
-        q.bulk = nbuf; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
+      const int ti = direct_bulk_ti(q.hd, q.wd, c.tile, q.group);
+      if (direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, c.tile, q.group, c.nbuf, ti, &bpitch, &bshift, &bsmem) &&
+          bsmem <= (c.nbuf == 2 && !force_nbuf ? budget2 : budget1) && occupancy_direct_bulk(q.hk, ti, c.nbuf, bsmem) >= 1) {
+        q.bulk = c.nbuf; q.ti = ti; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
+        q.tile_h = c.tile; q.tiles_per_image = (q.hd + c.tile - 1) / c.tile;
       }
     }
   }
-  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.hd, q.bulk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
+  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.ti, q.bulk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);

@@ -194,7 +194,9 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
   const size_t src_sz = (size_t)p.hs * p.ws, ker_sz = (size_t)p.hk * p.wk, dst_sz = (size_t)p.hd * p.wd;
   const int group = p.group;
   const long units = group > 1 ? (p.n_images + group - 1) / group : p.n_images * p.tiles_per_image;
-  const int rows_max = p.tile_h + hk - 1, nelem = rows_max * pitch;   // staged rows / doubles per image slot
+  // staged rows per image slot: whole blocks of TI output rows, so that no window has to be clamped (the rows past the
+  // tile are zeros and feed only outputs that are not stored)
+  const int rows_max = (p.tile_h + TI - 1) / TI * TI + hk - 1, nelem = rows_max * pitch;
   const int bufsz = group * nelem;
   const int sc0 = p.off_w - (p.wk - 1);
   const int c_lo = max(0, sc0), c_hi = min(p.ws, sc0 + p.wd + p.wk - 1);   // copied columns of the source
@@ -222,7 +224,7 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
     if (p.tiles_per_image > 1) {
       // row tiles: the rows above / below the source change from tile to tile and may hold an earlier tile's data
       const int top = r_lo - sr0, bot = r_hi - sr0;   // staged rows [top, bot) are copied
-      for (int i = threadIdx.x; i < (top + rows - bot) * pitch; i += kDirectThreads) {
+      for (int i = threadIdx.x; i < (top + rows_max - bot) * pitch; i += kDirectThreads) {
         const int u = i / pitch, v = i - u * pitch;
         S[(u < top ? u : bot + (u - top)) * pitch + v] = 0.0;
       }
@@ -247,7 +249,6 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
     const int ng = group > 1 ? (int)min((long)group, p.n_images - img0) : 1;
     const int i0 = group > 1 ? 0 : (int)(work - img0 * p.tiles_per_image) * p.tile_h;
     const int th = min(p.tile_h, p.hd - i0);
-    const int rows = th + hk - 1;
     __syncthreads();   // the previous unit's readers are done with the other buffer (NBUF 2) / this buffer (NBUF 1) and kflip
     if (NBUF == 2) {
       if (work + gridDim.x < units) stage(work + gridDim.x, buf ^ 1);
@@ -280,11 +281,11 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
 #pragma unroll
       for (int t = 0; t < TI; ++t) acc[t] = 0.0;
       const double* col = S + (g * nelem + r0 * pitch + j + p.col_shift);
-      const int last = rows - 1 - r0;   // highest staged row of this window
+#pragma unroll 2
       for (int kc = 0; kc < p.wk; ++kc) {
         double w[TI + HK - 1];
 #pragma unroll
-        for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[min(u, last) * pitch + kc];
+        for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[u * pitch + kc];
         const double* kv = kflip + kc * hk_pad;
 #pragma unroll
         for (int kr = 0; kr < HK; ++kr) {
@@ -303,13 +304,30 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
 
 // Can the bulk-staged variant run this geometry?  Fills the staged pitch, the column shift and the bytes of shared
 // memory.  Conditions: every row copy starts and ends on a 16-byte boundary in global AND shared memory.
+// Output rows per thread of the bulk-staged kernel: the member of {8, 10, 12} that wastes the fewest thread-rows on a
+// work unit -- rows past the tile in its last block plus idle threads in the last round of tasks.  (100 rows: 13
+// blocks of 8 are 104 rows and 1300 tasks = 5.08 rounds of 256 threads, 81 % useful; 10 blocks of 10 are 1000 tasks =
+// 3.9 rounds, 98 %.  Measured at 100 x 100 (*) 7 x 7: 14.6 -> 15.7 M conv/s; 96 rows want 12, 64 rows 8.)
+int direct_bulk_ti(int hd, int wd, int tile_h, int group) {
+  if (hd < 8) return 1;
+  const int th = tile_h < hd ? tile_h : hd;
+  int best = 8;
+  double best_eff = 0.0;
+  for (int ti : {8, 10, 12}) {
+    const long tasks = (long)((th + ti - 1) / ti) * wd * group;
+    const double eff = (double)th * wd * group / ((double)((tasks + kDirectThreads - 1) / kDirectThreads) * kDirectThreads * ti);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best = ti; }
+  }
+  return best;
+}
+
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
-                          int nbuf, int* pitch, int* col_shift, size_t* smem) {
+                          int nbuf, int ti, int* pitch, int* col_shift, size_t* smem) {
   if (hk < 1 || hk > kMaxDirectHK || (ws & 1)) return false;
   if (group > 1 && (((size_t)hs * ws) & 1)) return false;     // every image of a group starts 16-byte aligned
   const int sc0 = off_w - (wk - 1), cols = wd + wk - 1;
   const int c_lo = sc0 > 0 ? sc0 : 0, c_hi = ws < sc0 + cols ? ws : sc0 + cols;
-  const int rows = tile_h + hk - 1;
+  const int rows = (tile_h + ti - 1) / ti * ti + hk - 1;   // as direct_bulk_kernel pads them
   if (c_hi <= c_lo) return false;
   if ((c_lo & 1) || ((c_hi - c_lo) & 1)) return false;        // source side: ws is even, so rows start aligned
   const int shift = (c_lo - sc0) & 1;                          // destination side: staged column c_lo - sc0 + shift is even
@@ -363,15 +381,20 @@ static direct_fn direct_bulk_pick(int hk) {
   }
   return nullptr;
 }
-// tall: 8 output rows per thread; else (1-D rows, images shorter than 8 rows) one
-static direct_fn direct_bulk_variant(int hk, int nbuf, bool tall) {
-  if (tall) return nbuf == 2 ? direct_bulk_pick<2, 8>(hk) : direct_bulk_pick<1, 8>(hk);
-  return nbuf == 2 ? direct_bulk_pick<2, 1>(hk) : direct_bulk_pick<1, 1>(hk);
+// ti: output rows per thread (direct_bulk_ti)
+static direct_fn direct_bulk_variant(int hk, int nbuf, int ti) {
+  switch (ti) {
+    case 8: return nbuf == 2 ? direct_bulk_pick<2, 8>(hk) : direct_bulk_pick<1, 8>(hk);
+    case 10: return nbuf == 2 ? direct_bulk_pick<2, 10>(hk) : direct_bulk_pick<1, 10>(hk);
+    case 12: return nbuf == 2 ? direct_bulk_pick<2, 12>(hk) : direct_bulk_pick<1, 12>(hk);
+    case 1: return nbuf == 2 ? direct_bulk_pick<2, 1>(hk) : direct_bulk_pick<1, 1>(hk);
+  }
+  return nullptr;
 }
 
-int occupancy_direct_bulk(int hk, int hd, int nbuf, size_t smem) {
+int occupancy_direct_bulk(int hk, int ti, int nbuf, size_t smem) {
   int n = 0;
-  direct_fn fn = direct_bulk_variant(hk, nbuf, hd >= 8);
+  direct_fn fn = direct_bulk_variant(hk, nbuf, ti);
   if (!fn) return 0;
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
@@ -380,7 +403,7 @@ int occupancy_direct_bulk(int hk, int hd, int nbuf, size_t smem) {
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
   if (p.bulk) {
-    direct_fn fn = direct_bulk_variant(p.hk, p.bulk, p.hd >= 8);
+    direct_fn fn = direct_bulk_variant(p.hk, p.bulk, p.ti);
     cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     fn<<<grid, kDirectThreads, smem, st>>>(p);
     return cudaGetLastError();
