@@ -275,14 +275,16 @@ int auto_path(const Plan2D& pl, bool shared) {
   if (pl.h.n_ker > 16) t_direct *= 4.0;
   if (pl.mode == B2C_CIRCULAR_SAME) t_direct *= 1.35;   // wrapped source indices (profiles/r02_crossover_all_modes.csv)
   {
-    // bulk-staged variant (whole rows copied by the TMA engine, conv_direct.cu): streams at 6.4 TB/s plus 10.4 TFMA/s
-    // (fit of profiles/r02h_direct_bulk_staging.txt); the shapes it takes are the ones direct_bulk_geometry accepts
+    // bulk-staged variant (whole rows copied by the TMA engine, conv_direct.cu): streams at 6.0 TB/s plus 12.8 TFMA/s
+    // (least-squares fits of the direct column of profiles/r02_crossover_all_modes.csv by output height); the shapes it takes are the ones direct_bulk_geometry accepts
     int bp, bs;
     size_t bm;
     if (pl.mode != B2C_CIRCULAR_SAME && shared &&
         direct_bulk_geometry(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
                              pl.h.n_dst, 1, 1, direct_bulk_ti(pl.h.n_dst, pl.w.n_dst, pl.h.n_dst, 1), &bp, &bs, &bm) && bm <= 227 * 1024)
-      t_direct = pl.h.n_dst >= 8 ? bytes / 6.4e12 + fma / 10.4e12 + 0.3e-9
+      t_direct = pl.h.n_dst >= 48 ? bytes / 6.0e12 + fma / 12.8e12
+               : pl.h.n_dst >= 24 ? bytes / 6.8e12 + fma / 10.8e12 + 0.5e-9   // fewer rows: relatively more window loads, ragged task rounds
+               : pl.h.n_dst >= 8  ? bytes / 10e12 + fma / 8.5e12 + 0.3e-9
                                  : bytes / 5.2e12 + fma / 4.55e12 + std::min(0.9e-9, bytes * 9e-14);   // one row per thread
   }
   const double rows = (double)pl.h.n_src + pl.h.lin;
@@ -664,6 +666,8 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);
+  // bulk-staged row tiles: a grid that is a multiple of the tiles per image gives every CTA the same tile of each image
+  if (q.bulk && q.tiles_per_image > 1 && grid > q.tiles_per_image) grid -= grid % q.tiles_per_image;
   if (grid < 1) grid = 1;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   CUDA_TRY(g_timer.begin(st, &e0, &e1));
