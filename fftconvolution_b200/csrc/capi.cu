@@ -41,6 +41,7 @@ cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_
 bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, int ns_w);
 cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 int big2ds_ctas_per_sm();
+void big2ds_shape(int ctas, int* cols_strip, int* rows_chunk);
 bool tuned1d_has(int P);
 size_t tuned1d_scratch_elems(int P);
 cudaError_t launch_tuned1d(int P, int ns, int nk, int nd, int off, int n_in, int shift, const double* d_src, const double* d_ker,
@@ -414,8 +415,14 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
   q.src = d_src; q.ker = d_ker; q.ker_stride = shared ? 0 : (long)q.hk * q.wk; q.dst = d_dst; q.n_images = n;
   const int ctas = tuned ? big2ds_ctas_per_sm() : 1;
   if (tuned) {   // conv_big2ds.cu: fixed strips, S and K columns in two dense arrays
-    q.cols_strip = ctas == 2 ? 16 : 32; q.ldc = 2 * q.cols_strip;
-    q.rows_chunk = ctas == 2 ? 32 : 64;
+    big2ds_shape(ctas, &q.cols_strip, &q.rows_chunk);
+    q.ldc = 2 * q.cols_strip;
+    // Rows staged by the copy engine inside the row buffer (conv_big2ds.cu): needs 16-byte aligned rows and room for
+    // two half-spectrum rows (2 * (P/2 + 1) complex) in one buffer row
+    q.bulk_rows = !(q.ws & 1) && !(q.wk & 1) && !(((size_t)q.hs * q.ws) & 1) && !(q.ker_stride & 1) &&
+                  q.hk <= q.kwrap_h && q.wk <= q.kwrap_w && !(reinterpret_cast<size_t>(d_src) & 15) &&
+                  !(reinterpret_cast<size_t>(d_ker) & 15) && getenv("B2C_BIGS_NO_BULK_ROWS") == nullptr;
+    if (q.bulk_rows) q.ldw = Pw + 3;
   }
   const size_t smem = sizeof(cplx) * std::max((size_t)q.rows_chunk * q.ldw, (size_t)Ph * q.ldc);
   const int grid = (int)std::max<long>(1, std::min<long>(n, split ? group : (long)p->ctx->sms * ctas));

@@ -40,6 +40,13 @@ __device__ long long g_acc[16];   // debug variant: cycles accumulated per phase
 
 using namespace bulk;   // bulk_copy.cuh
 
+#ifndef B2C_BIGS_R0
+#define B2C_BIGS_R0 20     // first (twiddled) radix of the two-pass 200-point schedule (20 x 10: 1.74 M conv/s, 10 x 20: 1.63 M)
+#endif
+#ifndef B2C_BIGS_NT
+#define B2C_BIGS_NT 192    // threads per CTA in the two-CTAs-per-SM shape
+#endif
+
 template <int R> using Rbfly = BigBfly<R>;
 
 template <int P> struct TwTable;
@@ -52,7 +59,7 @@ __device__ __forceinline__ void stage(cplx* W, int es, int ls, int nlines, int w
                                       int nsplit = 1 << 30, int kjump = 0) {
   constexpr int M = N / R, PER_LINE = P / R, TSTEP = P / N;
   // 32 lines per warp task, or -- for strips of at most 16 lines -- two butterflies of 16 lines each
-  const int lpt = nlines <= 16 ? 16 : 32, subs = 32 / lpt;
+  const int lpt = nlines <= 8 ? 8 : nlines <= 16 ? 16 : 32, subs = 32 / lpt;
   const int ntrips = (nlines + lpt - 1) / lpt, total = PER_LINE * ntrips;
   for (int wt = warp; wt * subs < total; wt += nwarps) {
     const int task = wt * subs + lane / lpt;
@@ -110,7 +117,7 @@ struct Fft {
   // through shared memory fewer than forward-pass / product / backward-pass.
   static __device__ __forceinline__ void middle(cplx* W, int es, int ls, int nlines, int warp, int nwarps, int lane,
                                                 int koff, double scale) {
-    const int lpt = nlines <= 16 ? 16 : 32, subs = 32 / lpt;
+    const int lpt = nlines <= 8 ? 8 : nlines <= 16 ? 16 : 32, subs = 32 / lpt;
     const int ntrips = (nlines + lpt - 1) / lpt, total = R0 * ntrips;
     for (int wt = warp; wt * subs < total; wt += nwarps) {
       const int task = wt * subs + lane / lpt;
@@ -191,6 +198,24 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
     // ---------------- phase R: z_r = s_r + i*k_r, forward rows, Hermitian split -> slab
     for (int r0 = 0; r0 < rows_in; r0 += p.rows_chunk) {
       const int nr = min(p.rows_chunk, rows_in - r0);
+      if (p.bulk_rows) {
+        // The copy engine brings the chunk's source rows and kernel rows into the row buffer itself -- source row at the
+        // first P doubles of its buffer row, kernel row at the next P -- all rows in flight at once; each warp then
+        // expands its rows in place (reads into registers, __syncwarp, writes).  With one row per warp loaded by
+        // ordinary loads the phase sat on one HBM round trip per row: 45 k of 320 k cycles per image.
+        const int ns = max(0, min(nr, p.hs - r0)), nk = max(0, min(nr, hke - r0));
+        if (threadIdx.x == 0) mbar_expect_tx(bar, (unsigned)((ns * p.ws + nk * p.wk) * sizeof(double)));
+        for (int i = threadIdx.x; i < ns + nk; i += NT) {
+          const bool isk = i >= ns;
+          const int rr = isk ? i - ns : i;
+          double* to = reinterpret_cast<double*>(W + rr * ldw) + (isk ? P : 0);
+          if (isk) bulk_g2s(to, k + (size_t)(r0 + rr) * p.wk, (unsigned)(p.wk * sizeof(double)), bar);
+          else bulk_g2s(to, a + (size_t)(r0 + rr) * p.ws, (unsigned)(p.ws * sizeof(double)), bar);
+        }
+        mbar_wait(bar, bar_phase);
+        bar_phase ^= 1u;
+        B2C_T(14);
+      }
       for (int rr = warp; rr < nr; rr += nwarps) {
         const int r = r0 + rr;
         cplx* wrow = W + rr * ldw;
@@ -198,12 +223,24 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
         const double* krow = k + (size_t)r * p.wk;
         constexpr int NCH = (P + 31) / 32;       // all loads of a row are in flight before the first store
         cplx v[NCH];
+        if (p.bulk_rows) {
+          const double* srow = reinterpret_cast<const double*>(wrow);
+#pragma unroll
+          for (int u = 0; u < NCH; ++u) {
+            const int c = lane + 32 * u;
+            v[u] = make_double2(0.0, 0.0);
+            if (r < p.hs && c < p.ws) v[u].x = srow[c];
+            if (r < hke && c < wke) v[u].y = srow[P + c];
+          }
+          __syncwarp();   // every lane has read the staged row before any lane overwrites it
+        } else {
 #pragma unroll
         for (int u = 0; u < NCH; ++u) {
           const int c = lane + 32 * u;
           v[u] = make_double2(0.0, 0.0);
           if (r < p.hs && c < p.ws) v[u].x = __ldcs(arow + c);          // streamed once: evict first, keep the slabs in L2
           if (r < hke && c < wke) v[u].y = plain_kernel ? __ldcs(krow + c) : wrapped_tap(p, k, r, c);
+        }
         }
         // Source row and kernel row share one transform and are separated again right after it: the kernel
         // row is scaled to the source row's magnitude by a power of two (fft_device.cuh: balance_from_maxima;
@@ -240,7 +277,8 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
         }
       }
       __threadfence();          // slab rows must be in L2 and ordered before the copy engine reads them
-      fence_async_proxy();
+      fence_async_proxy_global();
+      fence_async_proxy();      // and the row buffer is next written by the copy engine
       __syncthreads();
       B2C_T(2);
     }
@@ -295,6 +333,23 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
     const int pairs = (p.hd + 1) / 2;
     for (int q0 = 0; q0 < pairs; q0 += p.rows_chunk) {
       const int nq = min(p.rows_chunk, pairs - q0);
+      if (p.bulk_rows) {
+        // The chunk's rows of Y travel by bulk copies as well: the slab is strip-major, so a row is one piece of
+        // nc * 16 bytes per strip; rows 2q and 2q+1 land side by side in buffer row q (HW complex each) and are
+        // combined in place below.
+        constexpr int NS = (P / 2 + 1 + CS - 1) / CS;    // strips
+        const int nrows = min(2 * nq, p.hd - 2 * q0);
+        if (threadIdx.x == 0) mbar_expect_tx(bar, (unsigned)(nrows * HW * sizeof(cplx)));
+        for (int i = threadIdx.x; i < nrows * NS; i += NT) {
+          const int ri = i / NS, s = i - ri * NS, v0 = s * CS, nc = min(CS, HW - v0);
+          const int row = p.off_h + 2 * q0 + ri;
+          bulk_g2s(W + (ri >> 1) * ldw + (ri & 1) * HW + v0, slab + (size_t)rows_total * v0 + (size_t)row * nc,
+                   (unsigned)(nc * sizeof(cplx)), bar);
+        }
+        mbar_wait(bar, bar_phase);
+        bar_phase ^= 1u;
+        B2C_T(15);
+      }
       for (int qq = warp; qq < nq; qq += nwarps) {
         const int i0 = 2 * (q0 + qq), i1 = i0 + 1;
         const int row0 = p.off_h + i0, row1 = p.off_h + i1;
@@ -309,14 +364,20 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
           pos[u] = -1;
           if (v < P) {
             const int vv = v < HW ? v : P - v;
-            const int v0 = vv & ~(CS - 1), nc = min(CS, HW - v0);
-            const cplx* blk = slab + (size_t)rows_total * v0 + (vv - v0);
-            y0[u] = __ldcg(blk + row0 * nc);   // written by the copy engine: read at L2, never from a stale L1 line
-            y1[u] = has1 ? __ldcg(blk + row1 * nc) : make_double2(0.0, 0.0);
+            if (p.bulk_rows) {
+              y0[u] = wrow[vv];
+              y1[u] = has1 ? wrow[HW + vv] : make_double2(0.0, 0.0);
+            } else {
+              const int v0 = vv & ~(CS - 1), nc = min(CS, HW - v0);
+              const cplx* blk = slab + (size_t)rows_total * v0 + (vv - v0);
+              y0[u] = __ldcg(blk + row0 * nc);   // written by the copy engine: read at L2, never from a stale L1 line
+              y1[u] = has1 ? __ldcg(blk + row1 * nc) : make_double2(0.0, 0.0);
+            }
             if (v >= HW) { y0[u].y = -y0[u].y; y1[u].y = -y1[u].y; }   // Hermitian mirror
             pos[u] = F::pos_of(v);
           }
         }
+        if (p.bulk_rows) __syncwarp();   // staged rows are read before the in-place combination overwrites them
 #pragma unroll
         for (int u = 0; u < NCH; ++u)
           if (pos[u] >= 0) wrow[pos[u]] = make_double2(y0[u].x - y1[u].y, y0[u].y + y1[u].x);
@@ -334,6 +395,7 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
           else        { for (int j = lane; j < p.wd; j += 32) __stcs(drow + j, wrow[j].x); }
         }
       }
+      fence_async_proxy();      // the row buffer may next be written by the copy engine
       __syncthreads();
       B2C_T(10);
     }
@@ -356,21 +418,28 @@ bool big2ds_has(int Ph, int Pw, const int* rad_h, int ns_h, const int* rad_w, in
 // threads with 16-column strips and 32-row chunks (one copies while the other transforms).  168 registers
 // per thread either way: the fused middle pass keeps 2 x 20 complex values.
 int big2ds_ctas_per_sm() {
-  static const int v = getenv("B2C_BIG_CTAS") ? atoi(getenv("B2C_BIG_CTAS")) : 2;   // measured: 1.53 vs 1.63 M conv/s
+  // measured: one CTA 1.53, two 1.63 M conv/s; three (160 threads) / four (128 threads) CTAs with 8-column strips and
+  // 16-row chunks 1.68 / 1.69 against 1.79 for two once the rows were bulk-staged (shapes removed again)
+  static const int v = getenv("B2C_BIG_CTAS") ? atoi(getenv("B2C_BIG_CTAS")) : 2;
   return v == 1 ? 1 : 2;
+}
+// strip width and rows per chunk of each shape
+void big2ds_shape(int ctas, int* cols_strip, int* rows_chunk) {
+  *cols_strip = ctas == 1 ? 32 : 16;
+  *rows_chunk = ctas == 1 ? 64 : 32;
+}
+
+template <int NT, int CTAS, int CS>
+static cudaError_t launch_shape(const BigParams& p, int grid, size_t smem, cudaStream_t st) {
+  auto kern = bigs::conv_kernel<200, B2C_BIGS_R0, 200 / B2C_BIGS_R0, NT, CTAS, CS>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  kern<<<grid, NT, smem, st>>>(p);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_conv_big2ds(const BigParams& p, int grid, size_t smem, cudaStream_t st) {
-  if (big2ds_ctas_per_sm() == 2) {
-    auto kern = bigs::conv_kernel<200, 10, 20, 192, 2, 16>;
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<grid, 192, smem, st>>>(p);
-  } else {
-    auto kern = bigs::conv_kernel<200, 10, 20, 384, 1, 32>;
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<grid, 384, smem, st>>>(p);
-  }
-  return cudaGetLastError();
+  if (big2ds_ctas_per_sm() == 1) return launch_shape<384, 1, 32>(p, grid, smem, st);
+  return launch_shape<B2C_BIGS_NT, 2, 16>(p, grid, smem, st);
 }
 
 }  // namespace b2c

@@ -55,6 +55,7 @@ struct BigParams {
   int cols_strip;    // half-spectrum columns per column-phase strip
   int ldc;           // row pitch (complex) of the column-phase buffer = 2*cols_strip (+1)
   int rows_y;        // rows of the linear result that are produced: off_h + hd
+  int bulk_rows;     // conv_big2ds.cu: source / kernel rows and result-spectrum rows enter the row buffer by bulk copies
   AxisDev ah, aw;
   double scale;
   const double* src;
