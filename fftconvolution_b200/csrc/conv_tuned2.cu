@@ -104,52 +104,83 @@ struct Geo {
 #undef B2C_T2_PERIMG
 #undef B2C_T2_KERNEL
 
-// Kernel spectrum K[pos][kk] = 0.5/(P*P) * DFT2(kernel)[u(kk)][v(pos)], straight from the taps.
+// Kernel spectrum K[pos][kk] = 0.5/(P*P) * DFT2(kernel)[u(kk)][v(pos)], straight from the taps, as a separable sum:
+// T1[b][kk] = sum_a tap[a][b] w^(u a), then K[pos][kk] = sum_b T1[b][kk] w^(v b).  Every CTA builds T1 for itself
+// (roots and folded taps staged in shared memory first) and then produces its own positions: the launch is a few
+// microseconds instead of the 34 us one 512-thread CTA took, which showed in batches of a few thousand images
+// (2 500 images of the headline shape: 160 us of convolutions behind 34 us of spectrum).
+constexpr int kKspecThreads = 256, kKspecStagedTaps = 4096;
 template <int R1, int R2>
-__global__ void __launch_bounds__(512, 1) kspec_kernel(const double* __restrict__ ker, int hk, int wk,
-                                                       const cplx* __restrict__ tw, cplx* __restrict__ out) {
+__global__ void __launch_bounds__(kKspecThreads) kspec_kernel(const double* __restrict__ ker, int hk, int wk,
+                                                              const cplx* __restrict__ tw, cplx* __restrict__ out) {
   typedef Geo<R1, R2> G;
   constexpr int P = G::P, NK = G::NK, KLD = G::KLD;
-  cplx* T1 = reinterpret_cast<cplx*>(b2c_smem_t2);  // [wke][NK]
   const int hke = min(hk, P), wke = min(wk, P);
-  for (int idx = threadIdx.x; idx < wke * NK; idx += blockDim.x) {
+  cplx* roots = reinterpret_cast<cplx*>(b2c_smem_t2);       // [P]
+  cplx* T1 = roots + P;                                     // [wke][NK]
+  double* taps = reinterpret_cast<double*>(T1 + wke * NK);  // [hke][wke], folded
+  const bool staged = hke * wke <= kKspecStagedTaps;        // larger kernels: folded taps are read from global memory
+  auto folded = [&](int a, int b) {
+    double tap = 0.0;   // taps congruent modulo the period add up (convolution_fftw.h:185-187)
+    for (int aa = a; aa < hk; aa += P)
+      for (int bb = b; bb < wk; bb += P) tap += ker[(size_t)aa * wk + bb];
+    return tap;
+  };
+  for (int i = threadIdx.x; i < P; i += kKspecThreads) roots[i] = tw[i];
+  if (staged)
+    for (int idx = threadIdx.x; idx < hke * wke; idx += kKspecThreads) taps[idx] = folded(idx / wke, idx % wke);
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < wke * NK; idx += kKspecThreads) {
     const int b = idx / NK, kk = idx - b * NK;
     const int u = G::freq_of_pos(G::rep_of(kk));
     cplx acc = make_double2(0.0, 0.0);
+    int ua = 0;   // (u * a) % P
     for (int a = 0; a < hke; ++a) {
-      double tap = 0.0;   // taps congruent modulo the period add up (convolution_fftw.h:185-187)
-      for (int aa = a; aa < hk; aa += P)
-        for (int bb = b; bb < wk; bb += P) tap += ker[(size_t)aa * wk + bb];
-      const cplx w = tw[(u * a) % P];
+      const double tap = staged ? taps[a * wke + b] : folded(a, b);
+      const cplx w = roots[ua];
       acc.x = fma(tap, w.x, acc.x);
       acc.y = fma(tap, w.y, acc.y);
+      ua += u; if (ua >= P) ua -= P;
     }
     T1[idx] = acc;
   }
   __syncthreads();
   const double scale = 0.5 / ((double)P * (double)P);
-  for (int idx = threadIdx.x; idx < P * NK; idx += blockDim.x) {
-    const int pos = idx / NK, kk = idx - pos * NK;
+  const int per = (P + gridDim.x - 1) / gridDim.x, pos0 = blockIdx.x * per, pos1 = min(P, pos0 + per);
+  for (int idx = threadIdx.x; idx < (pos1 - pos0) * NK; idx += kKspecThreads) {
+    const int pos = pos0 + idx / NK, kk = idx % NK;
     const int v = G::freq_of_pos(pos);
     cplx acc = make_double2(0.0, 0.0);
+    int vb = 0;   // (v * b) % P
     for (int b = 0; b < wke; ++b) {
       const cplx a = T1[b * NK + kk];
-      const cplx w = tw[(v * b) % P];
+      const cplx w = roots[vb];
       acc.x += a.x * w.x - a.y * w.y;
       acc.y += a.x * w.y + a.y * w.x;
+      vb += v; if (vb >= P) vb -= P;
     }
     out[pos * KLD + kk] = make_double2(acc.x * scale, acc.y * scale);
   }
 }
 
 template <int R1, int R2>
+static cudaError_t launch_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st) {
+  typedef Geo<R1, R2> G;
+  const int hke = hk < G::P ? hk : G::P, wke = wk < G::P ? wk : G::P;
+  const size_t ksmem = sizeof(cplx) * ((size_t)G::P + (size_t)wke * G::NK) +
+                       sizeof(double) * (size_t)(hke * wke <= kKspecStagedTaps ? hke * wke : 0);
+  cudaFuncSetAttribute(kspec_kernel<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmem);
+  // two positions per CTA; kernels close to the period make T1 expensive: fewer, fatter CTAs then
+  const int grid = (size_t)hke * wke > 1024 ? (G::P + 7) / 8 : (G::P + 1) / 2;
+  kspec_kernel<R1, R2><<<grid, kKspecThreads, ksmem, st>>>(d_ker, hk, wk, tw, out);
+  return cudaGetLastError();
+}
+
+template <int R1, int R2>
 cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, cudaStream_t st, int* launches) {
   typedef Geo<R1, R2> G;
-  const size_t ksmem = sizeof(cplx) * (size_t)(wk < G::P ? wk : G::P) * G::NK;
-  cudaFuncSetAttribute(kspec_kernel<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmem);
   if (d_ker) {   // nullptr: the spectrum of the previous call is still valid (single-call kernel cache)
-    kspec_kernel<R1, R2><<<1, 512, ksmem, st>>>(d_ker, hk, wk, p.tw, const_cast<cplx*>(p.kspec));
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = launch_kspec<R1, R2>(d_ker, hk, wk, p.tw, const_cast<cplx*>(p.kspec), st);
     if (e != cudaSuccess) return e;
     ++*launches;
   }
