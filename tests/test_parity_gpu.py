@@ -169,7 +169,10 @@ def test_strip_mode_many_images_per_cta(b2c, oracle, torch_cuda):
     against the oracle) -- catches stale slab / cache lines carried from one image to the next."""
     torch = torch_cuda
     rng = np.random.default_rng(77)
-    for (mode, hs, ws, hk, wk, n) in [(7, 100, 100, 100, 100, 2 * 148 + 41), (0, 120, 90, 70, 100, 148 + 19)]:
+    # the last two also run the compile-time 200 x 200 kernel: odd widths (rows loaded element-wise) and
+    # source / kernel of different heights with even widths (rows staged by bulk copies)
+    for (mode, hs, ws, hk, wk, n) in [(7, 100, 100, 100, 100, 2 * 148 + 41), (0, 120, 90, 70, 100, 148 + 19),
+                                      (7, 101, 99, 100, 101, 2 * 148 + 30), (0, 130, 150, 71, 50, 2 * 148 + 10)]:
         nproto = 3
         psrc, pker = rng.random((nproto, hs, ws)), rng.random((nproto, hk, wk))
         which = rng.integers(0, nproto, size=n)
