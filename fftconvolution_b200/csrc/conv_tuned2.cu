@@ -65,6 +65,20 @@ __device__ __forceinline__ void stg_if(double* ptr, double v, bool on) {
 #define B2C_T2_STG_IF(ptr, val, on) do { if (on) *(ptr) = (val); } while (0)
 #endif
 
+#ifndef B2C_T2_TP
+#define B2C_T2_TP 0    // A/B builds: period whose CTA size is overridden ...
+#define B2C_T2_TT 0    // ... and the size
+#endif
+// CTA size by period: 64 threads up to 48, 128 up to 80, 256 above (measured: P = 40: 74 -> 113 M conv/s, P = 80: 23.3 -> 28.5
+// against 256 threads), except where that size leaves a pass with a nearly empty last round of tasks (a pass hands
+// out lines x radix tasks in rounds of THREADS): measured with tools/gpu_periods.sh, ns per convolution
+//   P = 42: 11.5 -> 10.8 (160)   50: 16.7 -> 16.2 (160)   60: 22.3 -> 19.9 (96)   84: 52.3 -> 44.5 (160)
+//   100: 72.6 -> 69.1 (192)   126: 142 -> 134 (224);   no gain at 54, 64, 72, 80, 90, 96, 112, 120.
+constexpr int threads_of(int P) {
+  return P == 42 ? 160 : P == 50 ? 160 : P == 60 ? 96 : P == 84 ? 160 : P == 100 ? 192 : P == 126 ? 224
+       : P <= 48 ? 64 : P <= 80 ? 128 : 256;
+}
+
 template <int R1, int R2>
 struct Geo {
   static constexpr int P = R1 * R2;
@@ -74,9 +88,8 @@ struct Geo {
   static constexpr int LD = ((P + 2) | 1) + ((((P + 2) | 1) % 8 == 1) ? 2 : 0);   // odd, not == 1 (mod 8)
   static constexpr int KLD = (NK + 7) / 8 * 8;
   static constexpr int BPAD = KLD;
-  // CTA size follows the work per pass: small periods run many small CTAs per SM (measured: 64 threads up to
-  // P = 48, 128 up to 80; e.g. P = 40: 74 -> 113 M conv/s, P = 80: 23.3 -> 28.5 M conv/s against 256 threads)
-  static constexpr int THREADS = P <= 48 ? 64 : P <= 80 ? 128 : 256;
+  // CTA size follows the work per pass (threads_of above)
+  static constexpr int THREADS = P == B2C_T2_TP ? B2C_T2_TT : threads_of(P);
   static constexpr int A_LINES = THREADS / R2;
   static constexpr int A_ROUNDS = (NK + A_LINES - 1) / A_LINES;
   static constexpr int N0 = R2 / 2 + 1;          // half-spectrum columns in the p == 0 family
@@ -91,6 +104,9 @@ struct Geo {
     return kk == 0 ? P : (self_of(kk) ? P + 1 : (kk < N0 ? R2 - kk : P + R2 - 1 - rep_of(kk)));
   }
   static constexpr size_t smem_bytes = sizeof(cplx) * (size_t)HALF * LD;
+  // resident CTAs the register allocation is sized for: 128 registers per thread, or what shared memory allows
+  static constexpr int BY_SMEM = (int)((227 * 1024) / (smem_bytes + 1024)), BY_REGS = 512 / THREADS;
+  static constexpr int MIN_CTAS = BY_SMEM < BY_REGS ? (BY_SMEM < 1 ? 1 : BY_SMEM) : BY_REGS;
 };
 
 #define B2C_T2_PERIMG 0
