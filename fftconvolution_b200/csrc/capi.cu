@@ -306,7 +306,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   {
     static const struct { int P; double ns; } measured[] = {{16, 2.98}, {20, 4.22}, {24, 3.80}, {28, 4.35}, {32, 6.54}, {36, 8.42},
         {40, 9.52}, {48, 13.9}, {50, 17.5}, {54, 18.8}, {56, 20.2}, {60, 21.0}, {64, 23.9}, {70, 30.5}, {80, 39.7}, {100, 74.1},
-        {108, 77.3}, {112, 103.0}, {120, 128.0}};
+        {108, 77.3}, {112, 103.0}, {120, 128.0}, {140, 175.0}, {144, 180.0}, {160, 280.0}};
     for (const auto& m : measured)
       if (m.P == pl.h.P) t_tuned = m.ns * 1e-9;
   }

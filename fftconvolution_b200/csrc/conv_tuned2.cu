@@ -233,7 +233,8 @@ cudaError_t run_perimage(const Params& p, int sms, cudaStream_t st, int* launche
 // ---- the menu: square periods with a tuned kernel --------------------------------------------------
 #define B2C_T2_MENU(X)                                                                                         \
   X(8, 2) X(10, 2) X(8, 3) X(4, 7) X(8, 4) X(6, 6) X(8, 5) X(6, 7) X(8, 6) X(10, 5) X(6, 9) X(8, 7) X(10, 6) X(8, 8) \
-  X(10, 7) X(8, 9) X(10, 8) X(12, 7) X(10, 9) X(12, 8) X(10, 10) X(12, 9) X(14, 8) X(12, 10) X(14, 9) X(16, 8)
+  X(10, 7) X(8, 9) X(10, 8) X(12, 7) X(10, 9) X(12, 8) X(10, 10) X(12, 9) X(14, 8) X(12, 10) X(14, 9) X(16, 8) \
+  X(14, 10) X(16, 9) X(16, 10)
 
 bool tuned2_has(int P) {
   switch (P) {

@@ -165,7 +165,7 @@ static void axis_for_mode(int mode, int ns, int nk, AxisPlan& a) {
 }
 
 // Periods with a tuned shared-kernel kernel: square 2-D (conv_tuned108.cu, conv_tuned2.cu) and 1-D (conv_tuned1d.cu).
-static const int kMenu2D[] = {16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128};
+static const int kMenu2D[] = {16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128, 140, 144, 160};
 static const int kMenu1D[] = {128, 192, 256, 320, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2304, 2560, 3072, 4096, 4608, 5120, 6144, 8192};
 
 static bool in_menu(const int* menu, int n, int P) {
@@ -265,6 +265,15 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
       static const double alpha = 0.3 * (424.0 * fft_cost(108) + 12.0 * 108 * 108) / (108.0 * 108.0);
       const double c = alpha * pm * pm;
       if (c < best) { best = c; out.h.P = pm; out.w.P = pm; }
+    }
+    // beyond the shared-memory kernels: the compile-time 200 x 200 strip kernel (conv_big2ds.cu) takes every period
+    // up to 200 -- measured on 100 x 100 (*) k x k LINEAR_FULL: 560 ns per image at 200 against 880-1100 ns for the
+    // runtime-schedule strip kernel at 168, 180 and 192 (tools/bench_bigperiods.py)
+    // -- i.e. about half the generic model's cost at equal period; rectangles far from square keep their own periods
+    if (need > kMenu2D[sizeof kMenu2D / sizeof kMenu2D[0] - 1] && need <= 200) {
+      const double rows = (double)std::min(200, out.h.n_src) + std::min(200, out.h.lin);
+      const double c = 0.5 * (rows * fft_cost(200) + 2.0 * 200 * fft_cost(200) + 12.0 * 200 * 200);
+      if (c < best) { best = c; out.h.P = 200; out.w.P = 200; }
     }
   }
   // 1-D row signals: periods with a tuned kernel (conv_tuned1d.cu: three or four big-radix passes instead of

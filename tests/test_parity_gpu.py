@@ -172,7 +172,8 @@ def test_strip_mode_many_images_per_cta(b2c, oracle, torch_cuda):
     # the last two also run the compile-time 200 x 200 kernel: odd widths (rows loaded element-wise) and
     # source / kernel of different heights with even widths (rows staged by bulk copies)
     for (mode, hs, ws, hk, wk, n) in [(7, 100, 100, 100, 100, 2 * 148 + 41), (0, 120, 90, 70, 100, 148 + 19),
-                                      (7, 101, 99, 100, 101, 2 * 148 + 30), (0, 130, 150, 71, 50, 2 * 148 + 10)]:
+                                      (7, 101, 99, 100, 101, 2 * 148 + 30), (0, 130, 150, 71, 50, 2 * 148 + 10),
+                                      (0, 150, 100, 80, 60, 148 + 23)]:   # 229 x 159: runtime-schedule strip kernel
         nproto = 3
         psrc, pker = rng.random((nproto, hs, ws)), rng.random((nproto, hk, wk))
         which = rng.integers(0, nproto, size=n)
@@ -575,7 +576,7 @@ def test_tuned_square_period_family_vs_oracle(b2c, oracle, torch_cuda):
     with several modes / rectangular shapes and checked against the oracle and the any-size kernel."""
     torch = torch_cuda
     rng = np.random.default_rng(41)
-    menu = [16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 112, 120, 126, 128]
+    menu = [16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 112, 120, 126, 128, 140, 144, 160]
     hit = set()
     for P in menu:
         shapes = [(b2c.LINEAR_FULL, P - 9, P - 13, 10, 14),            # full length == P on both axes
@@ -616,7 +617,7 @@ def test_tuned_square_period_family_with_per_image_kernels(b2c, oracle, torch_cu
     transformed separately, like convolution_fftw.h:190-191, so 1e-12 must hold without any balancing)."""
     torch = torch_cuda
     rng = np.random.default_rng(43)
-    menu = [16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128]
+    menu = [16, 20, 24, 28, 32, 36, 40, 42, 48, 50, 54, 56, 60, 64, 70, 72, 80, 84, 90, 96, 100, 108, 112, 120, 126, 128, 140, 144, 160]
     hit = set()
     for P in menu:
         shapes = [(b2c.LINEAR_SAME, P - 4, P - 7, 9, 15), (b2c.LINEAR_FULL, P - 9, P - 13, 10, 14),
