@@ -264,7 +264,9 @@ bool make_plan(int mode, int hs, int ws, int hk, int wk, Plan2D& out) {
       // anchored at 0.3 x the generic model for the measured 108 x 108 case
       static const double alpha = 0.3 * (424.0 * fft_cost(108) + 12.0 * 108 * 108) / (108.0 * 108.0);
       const double c = alpha * pm * pm;
-      if (c < best) { best = c; out.h.P = pm; out.w.P = pm; }
+      // (periods below 16 are overhead-bound on the any-size kernel: 10 ns per image at 10 x 10 and 12 x 12 against
+      // 2.9 ns for the tuned 16 x 16, profiles/r02_crossover_all_modes.csv)
+      if (c < best || pm == 16) { best = std::min(best, c); out.h.P = pm; out.w.P = pm; }
     }
     // beyond the shared-memory kernels: the compile-time 200 x 200 strip kernel (conv_big2ds.cu) takes every period
     // up to 200 -- measured on 100 x 100 (*) k x k LINEAR_FULL: 560 ns per image at 200 against 880-1100 ns for the
