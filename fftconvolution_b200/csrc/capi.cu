@@ -52,7 +52,7 @@ bool tuned2_has(int P);
 size_t tuned2_kspec_bytes(int P);
 cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
                           int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker,
-                          double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
+                          double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches, int kmod_h, int kmod_w);
 cudaError_t launch_tuned2_perimage(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
                                    const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kscratch,
                                    const cplx* tw, int sms, cudaStream_t st, int* launches, long* slots);
@@ -485,8 +485,10 @@ bool big2d_fits(const b2c_plan* p) {
 
 // Shared-kernel plans with equal periods from the tuned menu (conv_tuned2.cu).
 bool tuned2_applies(const b2c_plan* p, const Plan2D& pl, int shared) {
+  // (kwrap < P: a CIRCULAR_SAME kernel larger than its source on a periodic-extension plan; the spectrum kernel folds
+  // the taps by the source extents)
   return shared && p->forced_path != B2C_PATH_FFT_GENERIC && pl.h.P == pl.w.P && tuned2_has(pl.h.P) &&
-         pl.h.fold == 0 && pl.w.fold == 0 && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
+         pl.h.fold == 0 && pl.w.fold == 0 && pl.h.kwrap <= pl.h.P && pl.w.kwrap <= pl.w.P;
 }
 
 int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const double* d_src, const double* d_ker, double* d_dst, long n,
@@ -496,7 +498,7 @@ int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const doubl
   // registers, but its 27-point transforms hold 108 of the 128 registers and it measured 15.1 against 15.7 M conv/s
   // (profiles/r02_pfa108_*).  Kept for A/B measurements and under the parity tests.
   const char* p108 = pl.h.P == 108 ? getenv("B2C_P108") : nullptr;   // read per call: the parity tests switch it
-  const bool pfa = p108 && !strcmp(p108, "pfa");
+  const bool pfa = p108 && !strcmp(p108, "pfa") && pl.h.kwrap == pl.h.P && pl.w.kwrap == pl.w.P;
   if (int rc = ensure_kspec(p, std::max(work_bytes(pl), std::max(tuned2_kspec_bytes(pl.h.P), pfa108_kspec_bytes())))) return rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   CUDA_TRY(g_timer.begin(st, &e0, &e1));
@@ -508,7 +510,7 @@ int run_tuned2(b2c_plan* p, const Plan2D& pl, const AxisTables& tww, const doubl
   else
   CUDA_TRY(launch_tuned2(pl.h.P, pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off,
                          pl.w.off, pl.h.n_in, pl.w.n_in, pl.h.src_shift, pl.w.src_shift, d_src, p->kspec_reuse ? nullptr : d_ker, d_dst, n,
-                         p->kspec, tww.tw, p->ctx->sms, st, &launches));
+                         p->kspec, tww.tw, p->ctx->sms, st, &launches, pl.h.kwrap, pl.w.kwrap));
   g_launches += launches;
   CUDA_TRY(g_timer.end(st, e0, e1));
   return 0;
@@ -818,8 +820,14 @@ int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kerne
     return fail(B2C_EINVAL, "b2c_plan_create: planning failed");
   }
   // CIRCULAR_SAME whose own period (exact, or folded when the size is not smooth) has no tuned kernel
-  if (mode == B2C_CIRCULAR_SAME && !plan_on_tuned_menu(p->pl))
+  if (mode == B2C_CIRCULAR_SAME && !plan_on_tuned_menu(p->pl)) {
     p->has_ext = make_plan_circular_ext(h_src, w_src, h_kernel, w_kernel, p->ext);
+    // a kernel that wraps around a small smooth source doubles the period on the extension plan: the any-size
+    // kernel at the exact period is then the faster one (30 x 30 (*) 100 x 100: 22 ns at period 30, 26 ns at 60)
+    if (p->has_ext && p->pl.h.fold == 0 && p->pl.w.fold == 0 && (h_kernel > h_src || w_kernel > w_src) &&
+        p->ext.w.P * 10 > std::max(p->pl.h.P, p->pl.w.P) * 16)
+      p->has_ext = false;
+  }
   if (!p->pl.empty && (long)p->pl.h.P * (long)work_ld(p->pl) >= (1L << 24)) {
     // Beyond the any-size kernel's 32-bit work-buffer offsets only strip mode runs (conv_big2d.cu):
     // it needs one row and a strip of one column pair in shared memory (227 KB) and no folding.

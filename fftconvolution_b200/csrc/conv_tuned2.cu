@@ -121,55 +121,49 @@ struct Geo {
 #undef B2C_T2_KERNEL
 
 // Kernel spectrum K[pos][kk] = 0.5/(P*P) * DFT2(kernel)[u(kk)][v(pos)], straight from the taps, as a separable sum:
-// T1[b][kk] = sum_a tap[a][b] w^(u a), then K[pos][kk] = sum_b T1[b][kk] w^(v b).  Every CTA builds T1 for itself
-// (roots and folded taps staged in shared memory first) and then produces its own positions: the launch is a few
-// microseconds instead of the 34 us one 512-thread CTA took, which showed in batches of a few thousand images
-// (2 500 images of the headline shape: 160 us of convolutions behind 34 us of spectrum).
-constexpr int kKspecThreads = 256, kKspecStagedTaps = 4096;
+// T1[b] = sum_a tap[a][b] w^(u a), then K[pos][kk] = sum_b T1[b] w^(v b).  One CTA per spectrum column kk: it builds
+// the T1 row of its own vertical frequency u(kk) (threads over the kernel columns b, taps read coalesced) and then all
+// P positions of that column (threads over pos).  No work is repeated between CTAs, so the cost is hke*wke + P*wke
+// complex FMAs per CTA whatever the kernel size (round 2 history: one 512-thread CTA for everything took 34 us at
+// 15 x 15 taps and 450 us at 100 x 100; sums run in the same order as there, so the spectra are bit-identical).
+// (mh, mw): the moduli the taps fold by (convolution_fftw.h:185-187: taps congruent modulo the period add up) -- the
+// period, or the source extents for a CIRCULAR_SAME kernel larger than its source computed by periodic extension
+// (planner.cpp: make_plan_circular_ext).
+constexpr int kKspecThreads = 256;
 template <int R1, int R2>
-__global__ void __launch_bounds__(kKspecThreads) kspec_kernel(const double* __restrict__ ker, int hk, int wk,
+__global__ void __launch_bounds__(kKspecThreads) kspec_kernel(const double* __restrict__ ker, int hk, int wk, int mh, int mw,
                                                               const cplx* __restrict__ tw, cplx* __restrict__ out) {
   typedef Geo<R1, R2> G;
-  constexpr int P = G::P, NK = G::NK, KLD = G::KLD;
-  const int hke = min(hk, P), wke = min(wk, P);
-  cplx* roots = reinterpret_cast<cplx*>(b2c_smem_t2);       // [P]
-  cplx* T1 = roots + P;                                     // [wke][NK]
-  double* taps = reinterpret_cast<double*>(T1 + wke * NK);  // [hke][wke], folded
-  const bool staged = hke * wke <= kKspecStagedTaps;        // larger kernels: folded taps are read from global memory
-  auto folded = [&](int a, int b) {
-    double tap = 0.0;   // taps congruent modulo the period add up (convolution_fftw.h:185-187)
-    for (int aa = a; aa < hk; aa += P)
-      for (int bb = b; bb < wk; bb += P) tap += ker[(size_t)aa * wk + bb];
-    return tap;
-  };
+  constexpr int P = G::P, KLD = G::KLD;
+  __shared__ cplx roots[P];
+  __shared__ cplx T1[P];
+  const int hke = min(hk, mh), wke = min(wk, mw);
+  const int kk = blockIdx.x;
+  const int u = G::freq_of_pos(G::rep_of(kk));
   for (int i = threadIdx.x; i < P; i += kKspecThreads) roots[i] = tw[i];
-  if (staged)
-    for (int idx = threadIdx.x; idx < hke * wke; idx += kKspecThreads) taps[idx] = folded(idx / wke, idx % wke);
   __syncthreads();
-  for (int idx = threadIdx.x; idx < wke * NK; idx += kKspecThreads) {
-    const int b = idx / NK, kk = idx - b * NK;
-    const int u = G::freq_of_pos(G::rep_of(kk));
+  for (int b = threadIdx.x; b < wke; b += kKspecThreads) {
     cplx acc = make_double2(0.0, 0.0);
     int ua = 0;   // (u * a) % P
     for (int a = 0; a < hke; ++a) {
-      const double tap = staged ? taps[a * wke + b] : folded(a, b);
+      double tap = 0.0;
+      for (int aa = a; aa < hk; aa += mh)
+        for (int bb = b; bb < wk; bb += mw) tap += ker[(size_t)aa * wk + bb];
       const cplx w = roots[ua];
       acc.x = fma(tap, w.x, acc.x);
       acc.y = fma(tap, w.y, acc.y);
       ua += u; if (ua >= P) ua -= P;
     }
-    T1[idx] = acc;
+    T1[b] = acc;
   }
   __syncthreads();
   const double scale = 0.5 / ((double)P * (double)P);
-  const int per = (P + gridDim.x - 1) / gridDim.x, pos0 = blockIdx.x * per, pos1 = min(P, pos0 + per);
-  for (int idx = threadIdx.x; idx < (pos1 - pos0) * NK; idx += kKspecThreads) {
-    const int pos = pos0 + idx / NK, kk = idx % NK;
+  for (int pos = threadIdx.x; pos < P; pos += kKspecThreads) {
     const int v = G::freq_of_pos(pos);
     cplx acc = make_double2(0.0, 0.0);
     int vb = 0;   // (v * b) % P
     for (int b = 0; b < wke; ++b) {
-      const cplx a = T1[b * NK + kk];
+      const cplx a = T1[b];
       const cplx w = roots[vb];
       acc.x += a.x * w.x - a.y * w.y;
       acc.y += a.x * w.y + a.y * w.x;
@@ -180,23 +174,19 @@ __global__ void __launch_bounds__(kKspecThreads) kspec_kernel(const double* __re
 }
 
 template <int R1, int R2>
-static cudaError_t launch_kspec(const double* d_ker, int hk, int wk, const cplx* tw, cplx* out, cudaStream_t st) {
+static cudaError_t launch_kspec(const double* d_ker, int hk, int wk, int mh, int mw, const cplx* tw, cplx* out, cudaStream_t st) {
   typedef Geo<R1, R2> G;
-  const int hke = hk < G::P ? hk : G::P, wke = wk < G::P ? wk : G::P;
-  const size_t ksmem = sizeof(cplx) * ((size_t)G::P + (size_t)wke * G::NK) +
-                       sizeof(double) * (size_t)(hke * wke <= kKspecStagedTaps ? hke * wke : 0);
-  cudaFuncSetAttribute(kspec_kernel<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmem);
-  // two positions per CTA; kernels close to the period make T1 expensive: fewer, fatter CTAs then
-  const int grid = (size_t)hke * wke > 1024 ? (G::P + 7) / 8 : (G::P + 1) / 2;
-  kspec_kernel<R1, R2><<<grid, kKspecThreads, ksmem, st>>>(d_ker, hk, wk, tw, out);
+  if (mh < 1 || mh > G::P) mh = G::P;
+  if (mw < 1 || mw > G::P) mw = G::P;
+  kspec_kernel<R1, R2><<<G::NK, kKspecThreads, 0, st>>>(d_ker, hk, wk, mh, mw, tw, out);
   return cudaGetLastError();
 }
 
 template <int R1, int R2>
-cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int sms, cudaStream_t st, int* launches) {
+cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int mh, int mw, int sms, cudaStream_t st, int* launches) {
   typedef Geo<R1, R2> G;
   if (d_ker) {   // nullptr: the spectrum of the previous call is still valid (single-call kernel cache)
-    cudaError_t e = launch_kspec<R1, R2>(d_ker, hk, wk, p.tw, const_cast<cplx*>(p.kspec), st);
+    cudaError_t e = launch_kspec<R1, R2>(d_ker, hk, wk, mh, mw, p.tw, const_cast<cplx*>(p.kspec), st);
     if (e != cudaSuccess) return e;
     ++*launches;
   }
@@ -251,14 +241,14 @@ size_t tuned2_kspec_bytes(int P) { return sizeof(cplx) * (size_t)P * (size_t)((P
 // kernel spectrum + convolution for a square period P from the menu; *launches += 2
 cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
                           int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker, double* d_dst, long n, cplx* kspec,
-                          const cplx* tw, int sms, cudaStream_t st, int* launches) {
+                          const cplx* tw, int sms, cudaStream_t st, int* launches, int kmod_h, int kmod_w) {
   t2::Params p;
   p.hs = hs; p.ws = ws; p.hd = hd; p.wd = wd; p.off_h = off_h; p.off_w = off_w;
   p.hs_in = hs_in; p.ws_in = ws_in; p.sh_h = sh_h; p.sh_w = sh_w;
   p.src = d_src; p.dst = d_dst; p.n_images = n; p.kspec = kspec; p.tw = tw;
   p.ker = nullptr; p.hk = hk; p.wk = wk; p.kscratch = nullptr;
   switch (P) {
-#define X(a, b) case (a) * (b): return t2::run<a, b>(p, d_ker, hk, wk, sms, st, launches);
+#define X(a, b) case (a) * (b): return t2::run<a, b>(p, d_ker, hk, wk, kmod_h, kmod_w, sms, st, launches);
     B2C_T2_MENU(X)
 #undef X
   }

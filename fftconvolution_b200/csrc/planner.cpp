@@ -180,17 +180,23 @@ bool plan_on_tuned_menu(const Plan2D& pl) {
   return pl.h.P == pl.w.P && in_menu(kMenu2D, sizeof kMenu2D / sizeof kMenu2D[0], pl.h.P);
 }
 
+// One axis of a CIRCULAR_SAME plan computed as the linear convolution of the periodically extended source (n_in =
+// ns + nke - 1 samples, the first nke - 1 a copy of the last ones) cropped at nke - 1.  A kernel longer than the source
+// wraps around it (taps congruent modulo ns add up, convolution_fftw.h:185-187): it counts with nke = ns taps and
+// kwrap = ns tells the spectrum kernel to fold the taps by ns instead of by the period.
 static void ext_axis(AxisPlan& a, int ns, int nk, int P) {
   a = AxisPlan();
+  const int nke = std::min(nk, ns);
   a.n_src = ns; a.n_ker = nk; a.n_dst = ns;
-  a.off = nk - 1; a.src_shift = nk - 1; a.n_in = ns + nk - 1;
-  a.lin = a.min_period = ns + nk - 1;
-  a.P = P; a.kwrap = P; a.n_ker_eff = nk;
+  a.off = nke - 1; a.src_shift = nke - 1; a.n_in = ns + nke - 1;
+  a.lin = a.min_period = ns + nke - 1;
+  a.P = P; a.kwrap = nk > ns ? ns : P; a.n_ker_eff = nke;
   finish_axis(a);
 }
 
 bool make_plan_circular_ext(int hs, int ws, int hk, int wk, Plan2D& out) {
-  if (hs < 1 || ws < 1 || hk < 1 || wk < 1 || hk > hs || wk > ws) return false;
+  if (hs < 1 || ws < 1 || hk < 1 || wk < 1) return false;
+  if (hs == 1 && wk > ws) return false;   // the tuned 1-D spectrum kernel folds by the period only
   out = Plan2D();
   out.mode = 4;
   out.ref_h_fft = hs; out.ref_w_fft = ws;
@@ -206,7 +212,7 @@ bool make_plan_circular_ext(int hs, int ws, int hk, int wk, Plan2D& out) {
     return false;
   }
   if (ws == 1) return false;   // columns are planned as rows by the caller
-  const int need = std::max(hs + hk - 1, ws + wk - 1);
+  const int need = std::max(hs + std::min(hk, hs) - 1, ws + std::min(wk, ws) - 1);
   for (int pm : kMenu2D) {
     if (pm < need) continue;
     ext_axis(out.h, hs, hk, pm);

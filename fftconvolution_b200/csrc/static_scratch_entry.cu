@@ -40,7 +40,7 @@ namespace b2c {
 // conv_tuned2.cu: kernel spectrum + convolution of a square menu period; allocates nothing
 cudaError_t launch_tuned2(int P, int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w,
                           int hs_in, int ws_in, int sh_h, int sh_w, const double* d_src, const double* d_ker,
-                          double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches);
+                          double* d_dst, long n, cplx* kspec, const cplx* tw, int sms, cudaStream_t st, int* launches, int kmod_h, int kmod_w);
 // capi.cu
 int set_last_error(int code, const char* text);
 }  // namespace b2c
@@ -159,7 +159,7 @@ extern "C" int b2c_convolve_batch_device_static(int mode, int h_src, int w_src, 
   // every call rewrites the whole spectrum before it is read (see the rules at the top of the file)
   int launches = 0;
   e = b2c::launch_tuned2(kPeriod, h_src, w_src, h_kernel, w_kernel, ah.n_dst, aw.n_dst, ah.off, aw.off, h_src, w_src, 0, 0,
-                         d_src, d_kernel, d_dst, n_images, spectrum, roots, d->sms, st, &launches);
+                         d_src, d_kernel, d_dst, n_images, spectrum, roots, d->sms, st, &launches, kPeriod, kPeriod);
   if (e != cudaSuccess) return cuda_fail("kernel launch", e);
   return 0;
 }
