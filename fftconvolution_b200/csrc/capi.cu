@@ -271,10 +271,15 @@ int auto_path(const Plan2D& pl, bool shared) {
   const double bytes = 8.0 * ((double)pl.h.n_src * pl.w.n_src + (double)pl.h.n_dst * pl.w.n_dst);
   double t_direct;
   const double per_image = shared ? 0.4e-9 : 4e-9;
-  if (pl.h.n_dst >= 8) t_direct = std::max(bytes / (pl.h.n_dst >= 64 ? 3.5e12 : 2.8e12), fma / 5.2e12) + per_image;
-  else t_direct = bytes / 3.4e12 + fma / 4.5e12 + (shared ? std::min(2e-9, bytes * 1.25e-13) : per_image);   // long rows: one tile per CTA
+  // element-wise staged kernel (8-byte cp.async per element): fits of tools/bench_direct_odd.py (odd widths) and of the
+  // CIRCULAR_SAME rows of profiles/r02_crossover_all_modes.csv (wrapped source indices)
+  if (pl.h.n_dst >= 8)
+    t_direct = (pl.mode == B2C_CIRCULAR_SAME ? bytes / 3.6e12 + fma / 8.4e12 : bytes / 4.6e12 + fma / 10.5e12) + (shared ? 0.6e-9 : 4e-9);
+  else {
+    t_direct = bytes / 3.4e12 + fma / 4.5e12 + (shared ? std::min(2e-9, bytes * 1.25e-13) : per_image);   // long rows: one tile per CTA
+    if (pl.mode == B2C_CIRCULAR_SAME) t_direct *= 1.35;
+  }
   if (pl.h.n_ker > 16) t_direct *= 4.0;
-  if (pl.mode == B2C_CIRCULAR_SAME) t_direct *= 1.35;   // wrapped source indices (profiles/r02_crossover_all_modes.csv)
   {
     // bulk-staged variant (whole rows copied by the TMA engine, conv_direct.cu): streams at 6.0 TB/s plus 12.8 TFMA/s
     // (least-squares fits of the direct column of profiles/r02_crossover_all_modes.csv by output height); the shapes it takes are the ones direct_bulk_geometry accepts
