@@ -381,9 +381,16 @@ int compute_balance(b2c_plan* p, const double* d_src, const double* d_ker, int s
 
 // Plans whose full complex work buffer exceeds shared memory run in strip mode (conv_big2d.cu):
 // row chunks / column strips in shared memory, half spectra through an L2-resident slab.
+// true when a batch of n images runs the persistent form (one CTA per image) rather than one launch per phase
+static bool big2d_persistent(const b2c_plan* p, long n) {
+  const long sms = p->ctx->sms, waves = (n + sms - 1) / sms;
+  return !(4 * n < 3 * waves * sms);
+}
+
+// plx: a periodic-extension plan at period 200 x 200 (CIRCULAR_SAME, planner.cpp: make_plan_circular_ext), else nullptr
 int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared, double* d_dst, long n,
-              cudaStream_t st) {
-  const Plan2D& pl = p->pl;
+              cudaStream_t st, const Plan2D* plx = nullptr) {
+  const Plan2D& pl = plx ? *plx : p->pl;
   const int Ph = pl.h.P, Pw = pl.w.P;
   // One CTA per image (persistent form) wastes the machine when the batch is not close to a whole
   // number of waves -- above all for a handful of large images.  Below 75 % wave efficiency the batch
@@ -399,6 +406,8 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
   q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
   q.hd = pl.h.n_dst; q.wd = pl.w.n_dst; q.off_h = pl.h.off; q.off_w = pl.w.off;
   q.kwrap_h = pl.h.kwrap; q.kwrap_w = pl.w.kwrap;
+  q.src_h = pl.h.n_src; q.src_w = pl.w.n_src;
+  if (plx) { q.hs = pl.h.n_in; q.ws = pl.w.n_in; q.sh_h = pl.h.src_shift; q.sh_w = pl.w.src_shift; }
   q.half_w = Pw / 2 + 1;
   q.ldw = Pw | 1;
   const int hke = std::min(q.hk, q.kwrap_h);
@@ -435,7 +444,7 @@ int run_big2d(b2c_plan* p, const double* d_src, const double* d_ker, int shared,
     // Rows staged by the copy engine inside the row buffer (conv_big2ds.cu): needs 16-byte aligned rows and room for
     // two half-spectrum rows (2 * (P/2 + 1) complex) in one buffer row
     q.bulk_rows = !(q.ws & 1) && !(q.wk & 1) && !(((size_t)q.hs * q.ws) & 1) && !(q.ker_stride & 1) &&
-                  q.hk <= q.kwrap_h && q.wk <= q.kwrap_w && !(reinterpret_cast<size_t>(d_src) & 15) &&
+                  q.hk <= q.kwrap_h && q.wk <= q.kwrap_w && !plx && !(reinterpret_cast<size_t>(d_src) & 15) &&
                   !(reinterpret_cast<size_t>(d_ker) & 15) && getenv("B2C_BIGS_NO_BULK_ROWS") == nullptr;
     if (q.bulk_rows) q.ldw = Pw + 3;
   }
@@ -570,6 +579,12 @@ int run_fft_path(b2c_plan* p, const double* d_src, const double* d_ker, int shar
                  long n, cudaStream_t st) {
   if (int rc = ensure_device_state(p)) return rc;
   const Plan2D& pl = p->pl;
+  if (p->has_ext && p->ext.h.P == 200 && p->ext.w.P == 200) {
+    // CIRCULAR_SAME of a non-smooth size whose extension needs 161..200 points: the 200 x 200 strip kernel, persistent
+    // form only (the phase kernels of the split form do not extend the source)
+    if (p->forced_path != B2C_PATH_FFT_GENERIC && big2d_persistent(p, n))
+      return run_big2d(p, d_src, d_ker, shared, d_dst, n, st, &p->ext);
+  } else
   if (p->has_ext && shared && p->forced_path != B2C_PATH_FFT_GENERIC) {   // CIRCULAR_SAME on a tuned menu period
     if (tuned2_applies(p, p->ext, shared)) return run_tuned2(p, p->ext, p->tw_ext, d_src, d_ker, d_dst, n, st);
     if (tuned1d_applies(p, p->ext, shared)) return run_tuned1d(p, p->ext, p->tw_ext, d_src, d_ker, d_dst, n, st);
@@ -832,6 +847,8 @@ int b2c_plan_create(b2c_plan** plan, int mode, int h_src, int w_src, int h_kerne
     if (p->has_ext && p->pl.h.fold == 0 && p->pl.w.fold == 0 && (h_kernel > h_src || w_kernel > w_src) &&
         p->ext.w.P * 10 > std::max(p->pl.h.P, p->pl.w.P) * 16)
       p->has_ext = false;
+    // the 200 x 200 extension (strip kernel, ~0.55 us per image) only pays against the folded plans of non-smooth sizes
+    if (p->has_ext && p->ext.h.P == 200 && p->pl.h.fold == 0 && p->pl.w.fold == 0) p->has_ext = false;
   }
   if (!p->pl.empty && (long)p->pl.h.P * (long)work_ld(p->pl) >= (1L << 24)) {
     // Beyond the any-size kernel's 32-bit work-buffer offsets only strip mode runs (conv_big2d.cu):

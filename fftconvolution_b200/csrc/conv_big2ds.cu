@@ -170,7 +170,8 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
   const int rows_in = max(p.hs, hke);
   const int HW = p.half_w, ldw = p.ldw;
   const bool plain_kernel = (p.hk <= p.kwrap_h) && (p.wk <= p.kwrap_w);
-  const size_t src_sz = (size_t)p.hs * p.ws, dst_sz = (size_t)p.hd * p.wd;
+  const size_t src_sz = (size_t)p.src_h * p.src_w, dst_sz = (size_t)p.hd * p.wd;
+  const bool shifted = (p.sh_h | p.sh_w) != 0;   // periodically extended source (CIRCULAR_SAME by linear convolution)
   // Per-CTA slab, strip-major: the block of strip v0 starts at rows_total * v0 and holds [hs][nc] S rows
   // followed by [hke][nc] K rows -- one contiguous run per transfer; the strip's Y[rows_y][nc] later
   // replaces the block in place.
@@ -238,7 +239,16 @@ __global__ void __launch_bounds__(NT, CTAS) conv_kernel(const __grid_constant__ 
         for (int u = 0; u < NCH; ++u) {
           const int c = lane + 32 * u;
           v[u] = make_double2(0.0, 0.0);
-          if (r < p.hs && c < p.ws) v[u].x = __ldcs(arow + c);          // streamed once: evict first, keep the slabs in L2
+          if (r < p.hs && c < p.ws) {
+            if (shifted) {
+              int sr = r - p.sh_h, sc = c - p.sh_w;   // shifts are below the source extents: one wrap
+              if (sr < 0) sr += p.src_h; else if (sr >= p.src_h) sr -= p.src_h;
+              if (sc < 0) sc += p.src_w; else if (sc >= p.src_w) sc -= p.src_w;
+              v[u].x = __ldg(a + (size_t)sr * p.src_w + sc);
+            } else {
+              v[u].x = __ldcs(arow + c);          // streamed once: evict first, keep the slabs in L2
+            }
+          }
           if (r < hke && c < wke) v[u].y = plain_kernel ? __ldcs(krow + c) : wrapped_tap(p, k, r, c);
         }
         }

@@ -56,6 +56,8 @@ struct BigParams {
   int ldc;           // row pitch (complex) of the column-phase buffer = 2*cols_strip (+1)
   int rows_y;        // rows of the linear result that are produced: off_h + hd
   int bulk_rows;     // conv_big2ds.cu: source / kernel rows and result-spectrum rows enter the row buffer by bulk copies
+  int src_h, src_w;  // conv_big2ds.cu: extents of the stored source; (hs, ws) are the input extents the transforms see --
+  int sh_h, sh_w;    //   larger by the shift when the source is extended periodically: input (r, c) = source ((r - sh_h) mod src_h, (c - sh_w) mod src_w)
   AxisDev ah, aw;
   double scale;
   const double* src;

@@ -219,6 +219,11 @@ bool make_plan_circular_ext(int hs, int ws, int hk, int wk, Plan2D& out) {
     ext_axis(out.w, ws, wk, pm);
     return true;
   }
+  if (need <= 200) {   // the compile-time 200 x 200 strip kernel (conv_big2ds.cu) reads periodically extended sources too
+    ext_axis(out.h, hs, hk, 200);
+    ext_axis(out.w, ws, wk, 200);
+    return true;
+  }
   return false;
 }
 

@@ -173,12 +173,15 @@ def test_strip_mode_many_images_per_cta(b2c, oracle, torch_cuda):
     # source / kernel of different heights with even widths (rows staged by bulk copies)
     for (mode, hs, ws, hk, wk, n) in [(7, 100, 100, 100, 100, 2 * 148 + 41), (0, 120, 90, 70, 100, 148 + 19),
                                       (7, 101, 99, 100, 101, 2 * 148 + 30), (0, 130, 150, 71, 50, 2 * 148 + 10),
-                                      (0, 150, 100, 80, 60, 148 + 23)]:   # 229 x 159: runtime-schedule strip kernel
+                                      (0, 150, 100, 80, 60, 148 + 23),    # 229 x 159: runtime-schedule strip kernel
+                                      # CIRCULAR_SAME of non-smooth sizes by periodic extension on the 200 x 200 kernel,
+                                      # kernel larger than / smaller than the source
+                                      (4, 97, 97, 99, 99, 148 + 20), (4, 89, 93, 80, 85, 148 + 5)]:
         nproto = 3
         psrc, pker = rng.random((nproto, hs, ws)), rng.random((nproto, hk, wk))
         which = rng.integers(0, nproto, size=n)
         p = b2c.Plan(mode, hs, ws, hk, wk)
-        assert not p.info()["work_in_smem"]
+        assert mode == 4 or not p.info()["work_in_smem"]
         p.set_path(b2c.PATH_FFT)
         d_src = torch.from_numpy(psrc[which]).cuda()
         d_ker = torch.from_numpy(pker[which]).cuda()

@@ -3,7 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, fftconvolution_b200 as b2c
 torch.cuda.set_device(0)
-for s, k in [(43, 61), (61, 70), (61, 100), (80, 100), (97, 99), (30, 100)]:
+for s, k in [(43, 61), (61, 70), (61, 100), (80, 100), (97, 99), (97, 80), (89, 85), (30, 100)]:
     p = b2c.Plan(b2c.CIRCULAR_SAME, s, s, k, k); p.set_path(b2c.PATH_FFT)
     n = 4096
     src = torch.rand((n, s, s), dtype=torch.float64, device="cuda"); ker = torch.rand((k, k), dtype=torch.float64, device="cuda")
