@@ -69,6 +69,12 @@ __device__ __forceinline__ void stg_if(double* ptr, double v, bool on) {
 #define B2C_T2_TP 0    // A/B builds: period whose CTA size is overridden ...
 #define B2C_T2_TT 0    // ... and the size
 #endif
+#ifndef B2C_T2_TP_MINB
+#define B2C_T2_TP_MINB 0   // A/B builds: resident CTAs the registers of that period's kernel are sized for (0: by formula)
+#endif
+#ifndef B2C_T2_TP_TWMEM
+#define B2C_T2_TP_TWMEM 0  // A/B builds: that period reads its twiddles from memory instead of keeping them in registers
+#endif
 // CTA size by period: 64 threads up to 48, 128 up to 80, 256 above (measured: P = 40: 74 -> 113 M conv/s, P = 80: 23.3 -> 28.5
 // against 256 threads), except where that size leaves a pass with a nearly empty last round of tasks (a pass hands
 // out lines x radix tasks in rounds of THREADS): measured with tools/gpu_periods.sh, ns per convolution
@@ -93,7 +99,7 @@ struct Geo {
   static constexpr int A_LINES = THREADS / R2;
   static constexpr int A_ROUNDS = (NK + A_LINES - 1) / A_LINES;
   static constexpr int N0 = R2 / 2 + 1;          // half-spectrum columns in the p == 0 family
-  static constexpr bool TW_IN_REGS = R1 <= 12;   // R1-1 complex twiddles per thread
+  static constexpr bool TW_IN_REGS = R1 <= 12 && !(B2C_T2_TP_TWMEM && P == B2C_T2_TP);   // R1-1 complex twiddles per thread
   static_assert(R1 % 2 == 0, "the column packing pairs c with c + P/2 = c + R2 * R1/2");
   static __host__ __device__ constexpr int freq_of_pos(int pos) { return pos / R2 + R1 * (pos % R2); }
   static __host__ __device__ constexpr int rep_of(int kk) { return kk < N0 ? kk : R2 + (kk - N0); }
@@ -106,7 +112,7 @@ struct Geo {
   static constexpr size_t smem_bytes = sizeof(cplx) * (size_t)HALF * LD;
   // resident CTAs the register allocation is sized for: 128 registers per thread, or what shared memory allows
   static constexpr int BY_SMEM = (int)((227 * 1024) / (smem_bytes + 1024)), BY_REGS = 512 / THREADS;
-  static constexpr int MIN_CTAS = BY_SMEM < BY_REGS ? (BY_SMEM < 1 ? 1 : BY_SMEM) : BY_REGS;
+  static constexpr int MIN_CTAS = (B2C_T2_TP_MINB && P == B2C_T2_TP) ? B2C_T2_TP_MINB : BY_SMEM < BY_REGS ? (BY_SMEM < 1 ? 1 : BY_SMEM) : BY_REGS;
 };
 
 #define B2C_T2_PERIMG 0
