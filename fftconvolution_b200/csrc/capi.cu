@@ -29,7 +29,7 @@ int occupancy_conv_perimage(int threads, size_t smem, bool in_smem);
 // conv_direct.cu
 size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int group = 1);
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st);
-int occupancy_direct(int hk, int hd, bool wrap, size_t smem);
+int occupancy_direct(int hk, int ti, bool wrap, size_t smem);
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
                           int nbuf, int ti, int* pitch, int* col_shift, size_t* smem);
 int direct_bulk_ti(int hd, int wd, int tile_h, int group);
@@ -274,7 +274,7 @@ int auto_path(const Plan2D& pl, bool shared) {
   // element-wise staged kernel (8-byte cp.async per element): fits of tools/bench_direct_odd.py (odd widths) and of the
   // CIRCULAR_SAME rows of profiles/r02_crossover_all_modes.csv (wrapped source indices)
   if (pl.h.n_dst >= 8)
-    t_direct = (pl.mode == B2C_CIRCULAR_SAME ? bytes / 3.6e12 + fma / 8.4e12 : bytes / 4.6e12 + fma / 10.5e12) + (shared ? 0.6e-9 : 4e-9);
+    t_direct = (pl.mode == B2C_CIRCULAR_SAME ? bytes / 3.85e12 + fma / 9.0e12 : bytes / 4.9e12 + fma / 11.3e12) + (shared ? 0.6e-9 : 4e-9);
   else {
     t_direct = bytes / 3.4e12 + fma / 4.5e12 + (shared ? std::min(2e-9, bytes * 1.25e-13) : per_image);   // long rows: one tile per CTA
     if (pl.mode == B2C_CIRCULAR_SAME) t_direct *= 1.35;
@@ -678,6 +678,7 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   }
   size_t smem = direct_smem_bytes(q.hk, q.wk, q.wd, tile, &spw, q.group);
   q.sp_w = spw;
+  q.ti = direct_bulk_ti(q.hd, q.wd, q.tile_h, q.group);   // task rows per thread (the bulk-staged variant may re-tile below)
   // whole images, no wrapping, aligned rows: the bulk-staged variant (source rows copied by the TMA engine)
   static const bool no_bulk = getenv("B2C_DIRECT_NO_BULK") != nullptr;   // A/B measurements
   static const int force_nbuf = getenv("B2C_DIRECT_NBUF") ? atoi(getenv("B2C_DIRECT_NBUF")) : 0;
@@ -701,7 +702,7 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
       }
     }
   }
-  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.ti, q.bulk, smem) : occupancy_direct(q.hk, q.hd, q.wrap_h > 0, smem);
+  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.ti, q.bulk, smem) : occupancy_direct(q.hk, q.ti, q.wrap_h > 0, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);

@@ -353,20 +353,25 @@ size_t direct_smem_bytes(int hk, int wk, int wd, int tile_h, int* sp_w_out, int 
 typedef void (*direct_fn)(const DirectParams);
 
 template <int HK>
-static direct_fn pick(bool tall, bool wrap) {
-  if (wrap) return tall ? direct_kernel<HK, 8, true> : direct_kernel<HK, 1, true>;
-  return tall ? direct_kernel<HK, 8, false> : direct_kernel<HK, 1, false>;
+static direct_fn pick(int ti, bool wrap) {
+  if (HK == 0) ti = ti > 1 ? 8 : 1;   // run-time kernel height: two sizes only
+  switch (ti) {
+    case 10: return wrap ? direct_kernel<HK, (HK ? 10 : 8), true> : direct_kernel<HK, (HK ? 10 : 8), false>;
+    case 12: return wrap ? direct_kernel<HK, (HK ? 12 : 8), true> : direct_kernel<HK, (HK ? 12 : 8), false>;
+    case 1: return wrap ? direct_kernel<HK, 1, true> : direct_kernel<HK, 1, false>;
+  }
+  return wrap ? direct_kernel<HK, 8, true> : direct_kernel<HK, 8, false>;
 }
 
-static direct_fn direct_variant(int hk, int hd, bool wrap) {
-  const bool tall = hd >= 8;
+// ti: output rows per thread (direct_bulk_ti: 1, 8, 10 or 12)
+static direct_fn direct_variant(int hk, int ti, bool wrap) {
   switch (hk) {
-    case 1: return pick<1>(tall, wrap);   case 2: return pick<2>(tall, wrap);   case 3: return pick<3>(tall, wrap);   case 4: return pick<4>(tall, wrap);
-    case 5: return pick<5>(tall, wrap);   case 6: return pick<6>(tall, wrap);   case 7: return pick<7>(tall, wrap);   case 8: return pick<8>(tall, wrap);
-    case 9: return pick<9>(tall, wrap);   case 10: return pick<10>(tall, wrap); case 11: return pick<11>(tall, wrap); case 12: return pick<12>(tall, wrap);
-    case 13: return pick<13>(tall, wrap); case 14: return pick<14>(tall, wrap); case 15: return pick<15>(tall, wrap); case 16: return pick<16>(tall, wrap);
+    case 1: return pick<1>(ti, wrap);   case 2: return pick<2>(ti, wrap);   case 3: return pick<3>(ti, wrap);   case 4: return pick<4>(ti, wrap);
+    case 5: return pick<5>(ti, wrap);   case 6: return pick<6>(ti, wrap);   case 7: return pick<7>(ti, wrap);   case 8: return pick<8>(ti, wrap);
+    case 9: return pick<9>(ti, wrap);   case 10: return pick<10>(ti, wrap); case 11: return pick<11>(ti, wrap); case 12: return pick<12>(ti, wrap);
+    case 13: return pick<13>(ti, wrap); case 14: return pick<14>(ti, wrap); case 15: return pick<15>(ti, wrap); case 16: return pick<16>(ti, wrap);
   }
-  return pick<0>(tall, wrap);
+  return pick<0>(ti, wrap);
 }
 
 template <int NBUF, int TI>
@@ -408,15 +413,15 @@ cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStre
     fn<<<grid, kDirectThreads, smem, st>>>(p);
     return cudaGetLastError();
   }
-  direct_fn fn = direct_variant(p.hk, p.hd, p.wrap_h > 0);
+  direct_fn fn = direct_variant(p.hk, p.ti, p.wrap_h > 0);
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   fn<<<grid, kDirectThreads, smem, st>>>(p);
   return cudaGetLastError();
 }
 
-int occupancy_direct(int hk, int hd, bool wrap, size_t smem) {
+int occupancy_direct(int hk, int ti, bool wrap, size_t smem) {
   int n = 0;
-  direct_fn fn = direct_variant(hk, hd, wrap);
+  direct_fn fn = direct_variant(hk, ti, wrap);
   cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
   return n;
