@@ -211,6 +211,9 @@ struct b2c_plan {
   Plan2D ext;
   AxisTables tw_ext;
   int forced_path = B2C_PATH_AUTO;
+  // last launch configuration of the direct path (geometry, variant, grid): a repeated call with the same batch size
+  // and buffer alignment -- the reference benchmark's loop of single convolve() calls -- skips the search
+  struct DirectLaunch { bool valid = false; long n = 0; int shared = 0; unsigned align = 0; DirectParams q; size_t smem = 0; int grid = 0; } direct_cache;
   bool t1d_tables = false;   // conv_tuned1d.cu: the per-pass twiddle tables behind the kernel spectrum are filled
   bool strip_only = false;   // too large for the any-size kernel: B2C_PATH_FFT_GENERIC is refused
   // lazily created device state (one device per plan)
@@ -646,6 +649,17 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
                     long n, cudaStream_t st) {
   if (int rc = ensure_device_state(p)) return rc;
   const Plan2D& pl = p->pl;
+  const unsigned align = (unsigned)(reinterpret_cast<size_t>(d_src) & 15);
+  if (p->direct_cache.valid && p->direct_cache.n == n && p->direct_cache.shared == shared && p->direct_cache.align == align) {
+    DirectParams q = p->direct_cache.q;
+    q.src = d_src; q.ker = d_ker; q.dst = d_dst;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    CUDA_TRY(g_timer.begin(st, &e0, &e1));
+    CUDA_TRY(launch_direct(q, p->direct_cache.grid, p->direct_cache.smem, st));
+    ++g_launches;
+    CUDA_TRY(g_timer.end(st, e0, e1));
+    return 0;
+  }
   DirectParams q;
   memset(&q, 0, sizeof q);
   q.hs = pl.h.n_src; q.ws = pl.w.n_src; q.hk = pl.h.n_ker; q.wk = pl.w.n_ker;
@@ -709,6 +723,8 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   // bulk-staged row tiles: a grid that is a multiple of the tiles per image gives every CTA the same tile of each image
   if (q.bulk && q.tiles_per_image > 1 && grid > q.tiles_per_image) grid -= grid % q.tiles_per_image;
   if (grid < 1) grid = 1;
+  p->direct_cache.valid = true; p->direct_cache.n = n; p->direct_cache.shared = shared; p->direct_cache.align = align;
+  p->direct_cache.q = q; p->direct_cache.smem = smem; p->direct_cache.grid = grid;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   CUDA_TRY(g_timer.begin(st, &e0, &e1));
   CUDA_TRY(launch_direct(q, grid, smem, st));

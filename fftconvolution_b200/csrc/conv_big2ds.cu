@@ -19,6 +19,7 @@
 //   * source / kernel reads and result writes carry evict-first hints so that the slabs
 //     (148 x 323 KB) stay resident in the 126 MB L2.
 #include "bulk_copy.cuh"
+#include "launch_cache.h"
 #include "conv_params.h"
 #include "tw200_table.h"
 
@@ -442,7 +443,7 @@ void big2ds_shape(int ctas, int* cols_strip, int* rows_chunk) {
 template <int NT, int CTAS, int CS>
 static cudaError_t launch_shape(const BigParams& p, int grid, size_t smem, cudaStream_t st) {
   auto kern = bigs::conv_kernel<200, B2C_BIGS_R0, 200 / B2C_BIGS_R0, NT, CTAS, CS>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dyn_smem(reinterpret_cast<const void*>(kern), smem);
   kern<<<grid, NT, smem, st>>>(p);
   return cudaGetLastError();
 }

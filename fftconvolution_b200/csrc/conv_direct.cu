@@ -11,6 +11,7 @@
 // kMaxDirectHK use the general variant (one load per FMA), which only matters for forced-path
 // tests: the planner never picks the direct path there.
 #include "bulk_copy.cuh"
+#include "launch_cache.h"
 #include "conv_params.h"
 
 namespace b2c {
@@ -401,20 +402,19 @@ int occupancy_direct_bulk(int hk, int ti, int nbuf, size_t smem) {
   int n = 0;
   direct_fn fn = direct_bulk_variant(hk, nbuf, ti);
   if (!fn) return 0;
-  cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
+  n = cached_occupancy(reinterpret_cast<const void*>(fn), kDirectThreads, smem);
   return n;
 }
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
   if (p.bulk) {
     direct_fn fn = direct_bulk_variant(p.hk, p.bulk, p.ti);
-    cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(reinterpret_cast<const void*>(fn), smem);
     fn<<<grid, kDirectThreads, smem, st>>>(p);
     return cudaGetLastError();
   }
   direct_fn fn = direct_variant(p.hk, p.ti, p.wrap_h > 0);
-  cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dyn_smem(reinterpret_cast<const void*>(fn), smem);
   fn<<<grid, kDirectThreads, smem, st>>>(p);
   return cudaGetLastError();
 }
@@ -422,8 +422,7 @@ cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStre
 int occupancy_direct(int hk, int ti, bool wrap, size_t smem) {
   int n = 0;
   direct_fn fn = direct_variant(hk, ti, wrap);
-  cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kDirectThreads, smem);
+  n = cached_occupancy(reinterpret_cast<const void*>(fn), kDirectThreads, smem);
   return n;
 }
 

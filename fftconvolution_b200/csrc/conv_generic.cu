@@ -10,6 +10,7 @@
 // Per-image kernel: z = src + i*kernel in one transform; the two spectra are separated by
 //                   Hermitian symmetry inside the product (the reference's GSL back end uses the
 //                   same identity, convolution_gsl.h:174-206).
+#include "launch_cache.h"
 #include "conv_params.h"
 
 namespace b2c {
@@ -209,7 +210,7 @@ __global__ void __launch_bounds__(512, 1) conv_perimage_kernel(const __grid_cons
 // ---- host-visible launchers -------------------------------------------------------------------
 cudaError_t launch_kspec(const ConvParams& p, int threads, size_t smem, cudaStream_t st) {
   if (p.work_in_smem) {
-    cudaFuncSetAttribute(kspec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(reinterpret_cast<const void*>(kspec_kernel<true>), smem);
     kspec_kernel<true><<<1, threads, smem, st>>>(p);
   } else {
     kspec_kernel<false><<<1, threads, 0, st>>>(p);
@@ -219,7 +220,7 @@ cudaError_t launch_kspec(const ConvParams& p, int threads, size_t smem, cudaStre
 
 cudaError_t launch_conv_shared(const ConvParams& p, int grid, int threads, size_t smem, cudaStream_t st) {
   if (p.work_in_smem) {
-    cudaFuncSetAttribute(conv_shared_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(reinterpret_cast<const void*>(conv_shared_kernel<true>), smem);
     conv_shared_kernel<true><<<grid, threads, smem, st>>>(p);
   } else {
     conv_shared_kernel<false><<<grid, threads, 0, st>>>(p);
@@ -229,7 +230,7 @@ cudaError_t launch_conv_shared(const ConvParams& p, int grid, int threads, size_
 
 cudaError_t launch_conv_perimage(const ConvParams& p, int grid, int threads, size_t smem, cudaStream_t st) {
   if (p.work_in_smem) {
-    cudaFuncSetAttribute(conv_perimage_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(reinterpret_cast<const void*>(conv_perimage_kernel<true>), smem);
     conv_perimage_kernel<true><<<grid, threads, smem, st>>>(p);
   } else {
     conv_perimage_kernel<false><<<grid, threads, 0, st>>>(p);
@@ -240,10 +241,10 @@ cudaError_t launch_conv_perimage(const ConvParams& p, int grid, int threads, siz
 int occupancy_conv_shared(int threads, size_t smem, bool in_smem) {
   int n = 0;
   if (in_smem) {
-    cudaFuncSetAttribute(conv_shared_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, conv_shared_kernel<true>, threads, smem);
+    ensure_dyn_smem(reinterpret_cast<const void*>(conv_shared_kernel<true>), smem);
+    n = cached_occupancy(reinterpret_cast<const void*>(conv_shared_kernel<true>), threads, smem);
   } else {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, conv_shared_kernel<false>, threads, 0);
+    n = cached_occupancy(reinterpret_cast<const void*>(conv_shared_kernel<false>), threads, 0);
   }
   return n;
 }
@@ -251,10 +252,10 @@ int occupancy_conv_shared(int threads, size_t smem, bool in_smem) {
 int occupancy_conv_perimage(int threads, size_t smem, bool in_smem) {
   int n = 0;
   if (in_smem) {
-    cudaFuncSetAttribute(conv_perimage_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, conv_perimage_kernel<true>, threads, smem);
+    ensure_dyn_smem(reinterpret_cast<const void*>(conv_perimage_kernel<true>), smem);
+    n = cached_occupancy(reinterpret_cast<const void*>(conv_perimage_kernel<true>), threads, smem);
   } else {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, conv_perimage_kernel<false>, threads, 0);
+    n = cached_occupancy(reinterpret_cast<const void*>(conv_perimage_kernel<false>), threads, 0);
   }
   return n;
 }

@@ -18,6 +18,7 @@
 // Positions are padded by one slot per LAST-radix block so that the last pass (a thread owns a
 // contiguous block) is free of bank conflicts.
 #include "conv_params.h"
+#include "launch_cache.h"
 
 namespace b2c {
 
@@ -326,8 +327,8 @@ cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int b
   }
   auto kk = kspec_kernel<P, R0, R1, R2, R3>;
   auto ck = conv_kernel<P, R0, R1, R2, R3>;
-  cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
-  cudaFuncSetAttribute(ck, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
+  ensure_dyn_smem(reinterpret_cast<const void*>(kk), G::smem_bytes);
+  ensure_dyn_smem(reinterpret_cast<const void*>(ck), G::smem_bytes);
   Params pk = p;
   pk.src = d_ker; pk.ns = nk; pk.n_in = nk; pk.shift = 0; pk.n_signals = 1;
   if (d_ker) {   // nullptr: the spectrum of the previous call is still valid (single-call kernel cache)
@@ -337,7 +338,7 @@ cudaError_t run(const Params& p, const double* d_ker, int nk, cplx* kspec, int b
     ++*launches;
   }
   int occ = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ck, G::THREADS, G::smem_bytes);
+  occ = cached_occupancy(reinterpret_cast<const void*>(ck), G::THREADS, G::smem_bytes);
   if (occ < 1) return cudaErrorLaunchOutOfResources;
   const long pairs = (p.n_signals + 1) / 2;
   long grid = (long)sms * occ;

@@ -17,6 +17,7 @@
 // p == 0; frequencies 0 and P/2 are their own partners and park their second half in two spare
 // columns (P, P+1).
 #include "conv_params.h"
+#include "launch_cache.h"
 
 namespace b2c {
 
@@ -197,8 +198,7 @@ cudaError_t run(const Params& p, const double* d_ker, int hk, int wk, int mh, in
     ++*launches;
   }
   int occ = 0;
-  cudaFuncSetAttribute(conv_kernel<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_kernel<R1, R2>, G::THREADS, G::smem_bytes);
+  occ = cached_occupancy(reinterpret_cast<const void*>(conv_kernel<R1, R2>), G::THREADS, G::smem_bytes);
   if (occ < 1) return cudaErrorLaunchOutOfResources;
   long grid = (long)sms * occ;
   if (grid > p.n_images) grid = p.n_images;
@@ -213,8 +213,7 @@ template <int R1, int R2>
 cudaError_t run_perimage(const Params& p, int sms, cudaStream_t st, int* launches, long* grid_out) {
   typedef Geo<R1, R2> G;
   int occ = 0;
-  cudaFuncSetAttribute(conv_kernel_perimage<R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_kernel_perimage<R1, R2>, G::THREADS, G::smem_bytes);
+  occ = cached_occupancy(reinterpret_cast<const void*>(conv_kernel_perimage<R1, R2>), G::THREADS, G::smem_bytes);
   if (occ < 1) return cudaErrorLaunchOutOfResources;
   long grid = (long)sms * occ;
   if (grid_out) { *grid_out = grid; return cudaSuccess; }
