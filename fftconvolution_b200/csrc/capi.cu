@@ -33,7 +33,9 @@ int occupancy_direct(int hk, int ti, bool wrap, size_t smem);
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
                           int nbuf, int ti, int* pitch, int* col_shift, size_t* smem);
 int direct_bulk_ti(int hd, int wd, int tile_h, int group);
-int occupancy_direct_bulk(int hk, int ti, int nbuf, size_t smem);
+int occupancy_direct_bulk(int hk, int ti, int nbuf, size_t smem, bool odd);
+bool direct_bulk_geometry_odd(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
+                              int nbuf, int ti, int* pitch, size_t* smem);
 // conv_big2d.cu
 cudaError_t launch_conv_big2d(const BigParams& p, int grid, size_t smem, cudaStream_t st);
 cudaError_t launch_conv_big2d_split(const BigParams& p, size_t smem, cudaStream_t st, int* launches);
@@ -288,9 +290,12 @@ int auto_path(const Plan2D& pl, bool shared) {
     // (least-squares fits of the direct column of profiles/r02_crossover_all_modes.csv by output height); the shapes it takes are the ones direct_bulk_geometry accepts
     int bp, bs;
     size_t bm;
+    const int bti = direct_bulk_ti(pl.h.n_dst, pl.w.n_dst, pl.h.n_dst, 1);
     if (pl.mode != B2C_CIRCULAR_SAME && shared &&
-        direct_bulk_geometry(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
-                             pl.h.n_dst, 1, 1, direct_bulk_ti(pl.h.n_dst, pl.w.n_dst, pl.h.n_dst, 1), &bp, &bs, &bm) && bm <= 227 * 1024)
+        (direct_bulk_geometry(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
+                              pl.h.n_dst, 1, 1, bti, &bp, &bs, &bm) ||
+         direct_bulk_geometry_odd(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
+                                  pl.h.n_dst, 1, 1, bti, &bp, &bm)) && bm <= 227 * 1024)
       t_direct = pl.h.n_dst >= 48 ? bytes / 6.0e12 + fma / 12.8e12
                : pl.h.n_dst >= 24 ? bytes / 6.8e12 + fma / 10.8e12 + 0.5e-9   // fewer rows: relatively more window loads, ragged task rounds
                : pl.h.n_dst >= 8  ? bytes / 10e12 + fma / 8.5e12 + 0.3e-9
@@ -696,6 +701,7 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   // whole images, no wrapping, aligned rows: the bulk-staged variant (source rows copied by the TMA engine)
   static const bool no_bulk = getenv("B2C_DIRECT_NO_BULK") != nullptr;   // A/B measurements
   static const int force_nbuf = getenv("B2C_DIRECT_NBUF") ? atoi(getenv("B2C_DIRECT_NBUF")) : 0;
+  static const bool no_odd = getenv("B2C_DIRECT_NO_ODD") != nullptr;   // A/B measurements
   if (!no_bulk && q.wrap_h == 0 && q.wrap_w == 0 && (reinterpret_cast<size_t>(d_src) & 15) == 0) {
     // two tile buffers per CTA (the next unit's copies fly during this unit's arithmetic) when two such CTAs still
     // fit an SM; else two buffers of half an image where the halves are whole blocks of task rows (100 x 100 (*) 7 x 7:
@@ -703,20 +709,25 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
     struct Cand { int tile, nbuf; } cands[3] = {{q.tile_h, 2}, {0, 2}, {q.tile_h, 1}};
     if (q.tiles_per_image == 1 && q.group == 1 && q.hd % 2 == 0 && q.hd >= 32 &&
         (q.hd / 2) % direct_bulk_ti(q.hd, q.wd, q.hd / 2, 1) == 0 && n * 2 >= (long)p->ctx->sms * 2)
-      cands[1].tile = q.hd / 2;
+      cands[1].tile = q.hd / 2;   // (ragged halves, e.g. 99 rows as 50 + 49: 73 -> 70 % of roof at 3 x 3, not taken)
     for (const Cand& c : cands) {
       if (q.bulk || c.tile <= 0 || (force_nbuf && c.nbuf != force_nbuf)) continue;
       int bpitch = 0, bshift = 0;
       size_t bsmem = 0;
       const int ti = direct_bulk_ti(q.hd, q.wd, c.tile, q.group);
-      if (direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, c.tile, q.group, c.nbuf, ti, &bpitch, &bshift, &bsmem) &&
-          bsmem <= (c.nbuf == 2 && !force_nbuf ? budget2 : budget1) && occupancy_direct_bulk(q.hk, ti, c.nbuf, bsmem) >= 1) {
-        q.bulk = c.nbuf; q.ti = ti; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
+      bool ok = direct_bulk_geometry(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, c.tile, q.group, c.nbuf, ti, &bpitch, &bshift, &bsmem);
+      bool odd = false;
+      if (!ok && !no_odd && (q.ws & 1)) {   // odd widths: per-row column shift (conv_direct.cu, ODD)
+        ok = direct_bulk_geometry_odd(q.hs, q.ws, q.hk, q.wk, q.hd, q.wd, q.off_h, q.off_w, c.tile, q.group, c.nbuf, ti, &bpitch, &bsmem);
+        odd = ok; bshift = 0;
+      }
+      if (ok && bsmem <= (c.nbuf == 2 && !force_nbuf ? budget2 : budget1) && occupancy_direct_bulk(q.hk, ti, c.nbuf, bsmem, odd) >= 1) {
+        q.bulk = c.nbuf; q.odd = odd; q.ti = ti; q.sp_w = bpitch; q.col_shift = bshift; smem = bsmem;
         q.tile_h = c.tile; q.tiles_per_image = (q.hd + c.tile - 1) / c.tile;
       }
     }
   }
-  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.ti, q.bulk, smem) : occupancy_direct(q.hk, q.ti, q.wrap_h > 0, smem);
+  int occ = q.bulk ? occupancy_direct_bulk(q.hk, q.ti, q.bulk, smem, q.odd != 0) : occupancy_direct(q.hk, q.ti, q.wrap_h > 0, smem);
   if (occ < 1) return fail(B2C_ECUDA, "direct kernel cannot be resident (smem=%zu)", smem);
   const long total = q.group > 1 ? (n + q.group - 1) / q.group : n * q.tiles_per_image;
   int grid = (int)std::min<long>(total, (long)p->ctx->sms * occ);

@@ -182,7 +182,13 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_kernel(const __grid_
 // above / below the source are cleared per unit (they move with the tile).
 // The host selects this variant only when every copy is 16-byte aligned at both ends (direct_bulk_geometry).
 // NBUF = 2: two staged tiles per CTA -- the copies of the next work unit are in flight while this one is computed.
-template <int HK, int NBUF, int TI>
+// ODD: odd source widths.  Rows then start alternately on and off a 16-byte boundary.  Every staged row gets its own
+// column shift d in {0, 1} -- source column c of source row sr sits at staged column c - sc0 + d,
+// d = (element offset of the image + sr - sc0) & 1 -- so that the row minus one edge element IS a 16-byte aligned
+// bulk copy at both ends; the edge element (first or last of the row) follows as one 8-byte cp.async, and the one
+// staged column next to the row that another unit's shift may have used is cleared.  Whole rows only (c_lo = 0,
+// c_hi = ws: true for every mode).  The window loop walks even and odd staged rows through two pointers.
+template <int HK, int NBUF, int TI, bool ODD>
 __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __grid_constant__ DirectParams p) {
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(b2c_smem_direct);   // [2]
   double* kflip = reinterpret_cast<double*>(b2c_smem_direct + 16);   // [wk][hk_pad]: column-major, flipped
@@ -232,6 +238,21 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
       bulk::fence_async_proxy();   // fenced before the barrier that precedes the next copies into this buffer
     }
     // (copies may complete before the byte count is posted: the phase cannot end before thread 0 has arrived)
+    if (ODD) {
+      if (threadIdx.x == 0) bulk::mbar_expect_tx(&bars[buf], (unsigned)(p.ws - 1) * 8u * (unsigned)(nr * ng));
+      for (int i = threadIdx.x; i < nr * ng; i += kDirectThreads) {
+        const int g = i / nr, r = r_lo + (i - g * nr);
+        const size_t e = (size_t)(img0 + g) * src_sz + (size_t)r * p.ws;   // element offset of the row in the batch
+        const int par = (int)(e & 1);                                      // the row starts 8 bytes off a 16-byte boundary
+        const int dlt = par ^ (sc0 & 1);                                   // this row's column shift
+        double* row = S + g * nelem + (r - sr0) * pitch - sc0 + dlt;       // staged address of source column 0
+        const double* srow = p.src + e;
+        row[dlt ? -1 : p.ws] = 0.0;                                        // the edge column the other shift would use
+        cp_async8(row + (par ? 0 : p.ws - 1), srow + (par ? 0 : p.ws - 1), 8);
+        bulk::bulk_g2s(row + par, srow + par, (unsigned)(p.ws - 1) * 8u, &bars[buf]);
+      }
+      return;
+    }
     if (threadIdx.x == 0) bulk::mbar_expect_tx(&bars[buf], row_bytes * (unsigned)(nr * ng));
     const double* a = p.src + (size_t)img0 * src_sz;
     for (int i = threadIdx.x; i < nr * ng; i += kDirectThreads) {
@@ -267,7 +288,8 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
     }
     bulk::mbar_wait(&bars[buf], buf ? phase1 : phase0);   // (completes at once when the unit has no source rows)
     if (buf) phase1 ^= 1u; else phase0 ^= 1u;
-    if (load_kernel) __syncthreads();   // kflip was written by other threads
+    if (ODD) cp_async_wait_all();                 // this thread's edge elements
+    if (ODD || load_kernel) __syncthreads();      // edge elements, cleared columns and kflip were written by other threads
     const double* S = S0 + buf * bufsz;
     double* d = p.dst + (size_t)img0 * dst_sz;
     const int blocks = (th + TI - 1) / TI;
@@ -282,11 +304,16 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
 #pragma unroll
       for (int t = 0; t < TI; ++t) acc[t] = 0.0;
       const double* col = S + (g * nelem + r0 * pitch + j + p.col_shift);
+      // ODD: staged row r0 + u carries the column shift (k0 + u) & 1 (see stage): even rows through pe, odd through po
+      const int k0 = ODD ? (int)(((size_t)(img0 + g) * src_sz + (size_t)(i0 + p.off_h - (hk - 1) + r0 - (p.off_w - (p.wk - 1)))) & 1) : 0;
+      const double* pe = col + k0;
+      const double* po = col + pitch + (1 - k0);
+      const int pitch2 = 2 * pitch;
 #pragma unroll 2
       for (int kc = 0; kc < p.wk; ++kc) {
         double w[TI + HK - 1];
 #pragma unroll
-        for (int u = 0; u < TI + HK - 1; ++u) w[u] = col[u * pitch + kc];
+        for (int u = 0; u < TI + HK - 1; ++u) w[u] = ODD ? ((u & 1) ? po : pe)[(u >> 1) * pitch2 + kc] : col[u * pitch + kc];
         const double* kv = kflip + kc * hk_pad;
 #pragma unroll
         for (int kr = 0; kr < HK; ++kr) {
@@ -320,6 +347,23 @@ int direct_bulk_ti(int hd, int wd, int tile_h, int group) {
     if (eff > best_eff + 1e-9) { best_eff = eff; best = ti; }
   }
   return best;
+}
+
+// Geometry of the odd-width form (direct_bulk_kernel<..., ODD = true>): whole rows, one spare staged column for the
+// per-row shift.
+bool direct_bulk_geometry_odd(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
+                              int nbuf, int ti, int* pitch, size_t* smem) {
+  (void)hs; (void)hd; (void)off_h;
+  if (hk < 1 || hk > kMaxDirectHK || !(ws & 1) || ws < 3) return false;
+  const int sc0 = off_w - (wk - 1), cols = wd + wk - 1;
+  if (sc0 > 0 || sc0 + cols < ws) return false;                // whole rows are staged
+  const int hk_pad = (hk + 1) & ~1;
+  if ((wk * hk_pad) & 1) return false;                         // S itself starts 16-byte aligned behind kflip
+  const int rows = (tile_h + ti - 1) / ti * ti + hk - 1;
+  const int pt = (cols + 1 + 1) & ~1;
+  *pitch = pt;
+  *smem = 16 + sizeof(double) * ((size_t)wk * hk_pad + (size_t)nbuf * group * rows * pt);
+  return true;
 }
 
 bool direct_bulk_geometry(int hs, int ws, int hk, int wk, int hd, int wd, int off_h, int off_w, int tile_h, int group,
@@ -375,40 +419,44 @@ static direct_fn direct_variant(int hk, int ti, bool wrap) {
   return pick<0>(ti, wrap);
 }
 
-template <int NBUF, int TI>
+template <int NBUF, int TI, bool ODD>
 static direct_fn direct_bulk_pick(int hk) {
   switch (hk) {
-    case 1: return direct_bulk_kernel<1, NBUF, TI>;   case 2: return direct_bulk_kernel<2, NBUF, TI>;   case 3: return direct_bulk_kernel<3, NBUF, TI>;
-    case 4: return direct_bulk_kernel<4, NBUF, TI>;   case 5: return direct_bulk_kernel<5, NBUF, TI>;   case 6: return direct_bulk_kernel<6, NBUF, TI>;
-    case 7: return direct_bulk_kernel<7, NBUF, TI>;   case 8: return direct_bulk_kernel<8, NBUF, TI>;   case 9: return direct_bulk_kernel<9, NBUF, TI>;
-    case 10: return direct_bulk_kernel<10, NBUF, TI>; case 11: return direct_bulk_kernel<11, NBUF, TI>; case 12: return direct_bulk_kernel<12, NBUF, TI>;
-    case 13: return direct_bulk_kernel<13, NBUF, TI>; case 14: return direct_bulk_kernel<14, NBUF, TI>; case 15: return direct_bulk_kernel<15, NBUF, TI>;
-    case 16: return direct_bulk_kernel<16, NBUF, TI>;
+    case 1: return direct_bulk_kernel<1, NBUF, TI, ODD>;   case 2: return direct_bulk_kernel<2, NBUF, TI, ODD>;
+    case 3: return direct_bulk_kernel<3, NBUF, TI, ODD>;   case 4: return direct_bulk_kernel<4, NBUF, TI, ODD>;
+    case 5: return direct_bulk_kernel<5, NBUF, TI, ODD>;   case 6: return direct_bulk_kernel<6, NBUF, TI, ODD>;
+    case 7: return direct_bulk_kernel<7, NBUF, TI, ODD>;   case 8: return direct_bulk_kernel<8, NBUF, TI, ODD>;
+    case 9: return direct_bulk_kernel<9, NBUF, TI, ODD>;   case 10: return direct_bulk_kernel<10, NBUF, TI, ODD>;
+    case 11: return direct_bulk_kernel<11, NBUF, TI, ODD>; case 12: return direct_bulk_kernel<12, NBUF, TI, ODD>;
+    case 13: return direct_bulk_kernel<13, NBUF, TI, ODD>; case 14: return direct_bulk_kernel<14, NBUF, TI, ODD>;
+    case 15: return direct_bulk_kernel<15, NBUF, TI, ODD>; case 16: return direct_bulk_kernel<16, NBUF, TI, ODD>;
   }
   return nullptr;
 }
-// ti: output rows per thread (direct_bulk_ti)
-static direct_fn direct_bulk_variant(int hk, int nbuf, int ti) {
+template <bool ODD>
+static direct_fn direct_bulk_variant_o(int hk, int nbuf, int ti) {
   switch (ti) {
-    case 8: return nbuf == 2 ? direct_bulk_pick<2, 8>(hk) : direct_bulk_pick<1, 8>(hk);
-    case 10: return nbuf == 2 ? direct_bulk_pick<2, 10>(hk) : direct_bulk_pick<1, 10>(hk);
-    case 12: return nbuf == 2 ? direct_bulk_pick<2, 12>(hk) : direct_bulk_pick<1, 12>(hk);
-    case 1: return nbuf == 2 ? direct_bulk_pick<2, 1>(hk) : direct_bulk_pick<1, 1>(hk);
+    case 8: return nbuf == 2 ? direct_bulk_pick<2, 8, ODD>(hk) : direct_bulk_pick<1, 8, ODD>(hk);
+    case 10: return nbuf == 2 ? direct_bulk_pick<2, 10, ODD>(hk) : direct_bulk_pick<1, 10, ODD>(hk);
+    case 12: return nbuf == 2 ? direct_bulk_pick<2, 12, ODD>(hk) : direct_bulk_pick<1, 12, ODD>(hk);
+    case 1: return nbuf == 2 ? direct_bulk_pick<2, 1, ODD>(hk) : direct_bulk_pick<1, 1, ODD>(hk);
   }
   return nullptr;
+}
+// ti: output rows per thread (direct_bulk_ti); odd: the odd-width form
+static direct_fn direct_bulk_variant(int hk, int nbuf, int ti, bool odd) {
+  return odd ? direct_bulk_variant_o<true>(hk, nbuf, ti) : direct_bulk_variant_o<false>(hk, nbuf, ti);
 }
 
-int occupancy_direct_bulk(int hk, int ti, int nbuf, size_t smem) {
-  int n = 0;
-  direct_fn fn = direct_bulk_variant(hk, nbuf, ti);
+int occupancy_direct_bulk(int hk, int ti, int nbuf, size_t smem, bool odd) {
+  direct_fn fn = direct_bulk_variant(hk, nbuf, ti, odd);
   if (!fn) return 0;
-  n = cached_occupancy(reinterpret_cast<const void*>(fn), kDirectThreads, smem);
-  return n;
+  return cached_occupancy(reinterpret_cast<const void*>(fn), kDirectThreads, smem);
 }
 
 cudaError_t launch_direct(const DirectParams& p, int grid, size_t smem, cudaStream_t st) {
   if (p.bulk) {
-    direct_fn fn = direct_bulk_variant(p.hk, p.bulk, p.ti);
+    direct_fn fn = direct_bulk_variant(p.hk, p.bulk, p.ti, p.odd != 0);
     ensure_dyn_smem(reinterpret_cast<const void*>(fn), smem);
     fn<<<grid, kDirectThreads, smem, st>>>(p);
     return cudaGetLastError();

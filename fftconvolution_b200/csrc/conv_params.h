@@ -37,6 +37,7 @@ struct DirectParams {
   // bulk-staged variant (conv_direct.cu: direct_bulk_kernel): whole images, rows copied by the TMA engine
   int bulk;              // 0: element-wise staging; 1 / 2: bulk-staged with that many tile buffers per CTA
   int ti;                // output rows per thread of the bulk-staged kernel (direct_bulk_ti)
+  int odd;               // that kernel's odd-width form: per-row column shift, edge element by cp.async
   int col_shift;         // staged column of source column c is c - (off_w - (wk - 1)) + col_shift (keeps copies 16-byte aligned)
   const double* src;
   const double* ker;
