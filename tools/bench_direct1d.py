@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, fftconvolution_b200 as b2c
 torch.cuda.set_device(0)
 tag = "nobulk" if os.environ.get("B2C_DIRECT_NO_BULK") else "bulk"
-for mode, ns, nk in [(2, 4096, 3), (2, 4096, 8), (2, 4096, 15), (0, 1000, 5), (2, 64, 15), (2, 256, 3), (3, 4096, 4)]:
+for mode, ns, nk in [(2, 4096, 3), (2, 4095, 3), (2, 4096, 8), (2, 4096, 15), (2, 4095, 15), (0, 1000, 5), (0, 999, 5), (2, 64, 15), (2, 63, 15), (2, 256, 3), (2, 255, 3), (3, 4096, 4)]:
     for col in (0, 1):
         shp = (ns, 1, nk, 1) if col else (1, ns, 1, nk)
         p = b2c.Plan(mode, *shp); p.set_path(b2c.PATH_DIRECT)
