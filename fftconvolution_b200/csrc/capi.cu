@@ -291,15 +291,17 @@ int auto_path(const Plan2D& pl, bool shared) {
     int bp, bs;
     size_t bm;
     const int bti = direct_bulk_ti(pl.h.n_dst, pl.w.n_dst, pl.h.n_dst, 1);
-    if (pl.mode != B2C_CIRCULAR_SAME && shared &&
+    const bool wraps = pl.mode == B2C_CIRCULAR_SAME;   // bulk-staged too when even-wide and the kernel fits the source: ~10 % slower
+    if ((!wraps || (!(pl.w.n_src & 1) && pl.h.n_ker <= pl.h.n_src && pl.w.n_ker <= pl.w.n_src)) && shared &&
         (direct_bulk_geometry(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
                               pl.h.n_dst, 1, 1, bti, &bp, &bs, &bm) ||
          direct_bulk_geometry_odd(pl.h.n_src, pl.w.n_src, pl.h.n_ker, pl.w.n_ker, pl.h.n_dst, pl.w.n_dst, pl.h.off, pl.w.off,
                                   pl.h.n_dst, 1, 1, bti, &bp, &bm)) && bm <= 227 * 1024)
-      t_direct = pl.h.n_dst >= 48 ? bytes / 6.0e12 + fma / 12.8e12
+      t_direct = (pl.h.n_dst >= 48 ? bytes / 6.0e12 + fma / 12.8e12
                : pl.h.n_dst >= 24 ? bytes / 6.8e12 + fma / 10.8e12 + 0.5e-9   // fewer rows: relatively more window loads, ragged task rounds
                : pl.h.n_dst >= 8  ? bytes / 10e12 + fma / 8.5e12 + 0.3e-9
-                                 : bytes / 5.2e12 + fma / 4.55e12 + std::min(0.9e-9, bytes * 9e-14);   // one row per thread
+                                 : bytes / 5.2e12 + fma / 4.55e12 + std::min(0.9e-9, bytes * 9e-14))   // one row per thread
+                 * (wraps ? 1.1 : 1.0);
   }
   const double rows = (double)pl.h.n_src + pl.h.lin;
   double cost = rows * fft_cost(pl.w.P) + 2.0 * pl.w.P * fft_cost(pl.h.P) + 12.0 * pl.h.P * pl.w.P;
@@ -702,7 +704,9 @@ int run_direct_path(b2c_plan* p, const double* d_src, const double* d_ker, int s
   static const bool no_bulk = getenv("B2C_DIRECT_NO_BULK") != nullptr;   // A/B measurements
   static const int force_nbuf = getenv("B2C_DIRECT_NBUF") ? atoi(getenv("B2C_DIRECT_NBUF")) : 0;
   static const bool no_odd = getenv("B2C_DIRECT_NO_ODD") != nullptr;   // A/B measurements
-  if (!no_bulk && q.wrap_h == 0 && q.wrap_w == 0 && (reinterpret_cast<size_t>(d_src) & 15) == 0) {
+  // (CIRCULAR_SAME: even widths and kernels no larger than the source, so that an index wraps at most once)
+  const bool wrap_ok = q.wrap_h == 0 || (!(q.ws & 1) && q.hk <= q.hs && q.wk <= q.ws && getenv("B2C_DIRECT_NO_WRAP_BULK") == nullptr);
+  if (!no_bulk && wrap_ok && (reinterpret_cast<size_t>(d_src) & 15) == 0) {
     // two tile buffers per CTA (the next unit's copies fly during this unit's arithmetic) when two such CTAs still
     // fit an SM; else two buffers of half an image where the halves are whole blocks of task rows (100 x 100 (*) 7 x 7:
     // 15.5 -> 16.4 M conv/s; ragged halves measured slower); else one buffer and two CTAs

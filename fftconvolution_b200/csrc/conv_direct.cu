@@ -225,6 +225,21 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
     const int r_lo = max(0, sr0), r_hi = min(p.hs, sr0 + rows);   // copied rows of the source
     const int nr = max(0, r_hi - r_lo);
     double* S = S0 + buf * bufsz;
+    if (!ODD && p.wrap_h > 0) {
+      // CIRCULAR_SAME (even widths): every staged row is a source row, (sr0 + u) mod hs, moved whole by one bulk copy;
+      // the wk - 1 columns in front of it are the END of the same row and follow as 8-byte cp.asyncs.  Nothing is zero.
+      const int L = p.wk - 1;
+      if (threadIdx.x == 0) bulk::mbar_expect_tx(&bars[buf], (unsigned)p.ws * 8u * (unsigned)(rows * ng));
+      for (int i = threadIdx.x; i < rows * ng; i += kDirectThreads) {
+        const int g = i / rows, u = i - g * rows;
+        const int r = wrap_index(sr0 + u, p.wrap_h);
+        const double* srow = p.src + ((size_t)(img0 + g) * src_sz + (size_t)r * p.ws);
+        double* row = S + g * nelem + u * pitch + L + p.col_shift;   // staged address of source column 0
+        bulk::bulk_g2s(row, srow, (unsigned)p.ws * 8u, &bars[buf]);
+        for (int m = 0; m < L; ++m) cp_async8(row - L + m, srow + p.ws - L + m, 8);
+      }
+      return;
+    }
     if (p.tiles_per_image > 1 && gridDim.x % p.tiles_per_image != 0) {
       // row tiles: the rows above / below the source change from tile to tile and may hold an earlier tile's data
       // (not when the grid is a multiple of the tiles per image: a CTA then meets the same tile of every image, its
@@ -288,8 +303,8 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
     }
     bulk::mbar_wait(&bars[buf], buf ? phase1 : phase0);   // (completes at once when the unit has no source rows)
     if (buf) phase1 ^= 1u; else phase0 ^= 1u;
-    if (ODD) cp_async_wait_all();                 // this thread's edge elements
-    if (ODD || load_kernel) __syncthreads();      // edge elements, cleared columns and kflip were written by other threads
+    if (ODD || p.wrap_h > 0) cp_async_wait_all();                 // this thread's edge / wrapped elements
+    if (ODD || p.wrap_h > 0 || load_kernel) __syncthreads();      // they, cleared columns and kflip were written by other threads
     const double* S = S0 + buf * bufsz;
     double* d = p.dst + (size_t)img0 * dst_sz;
     const int blocks = (th + TI - 1) / TI;
