@@ -3,4 +3,3 @@
 cd "$(dirname "$0")/.."
 timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
 for n in 512 2500 8192 65536; do timeout 300 python tools/quick_bench.py $n 20 | sed "s/^/n=$n /"; done
-for n in 512 2500 8192; do B2C_LIB_PATH=build/variants/kspec_old.so timeout 300 python tools/quick_bench.py $n 20 | sed "s/^/old n=$n /"; done
