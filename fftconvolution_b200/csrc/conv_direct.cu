@@ -26,6 +26,9 @@ __device__ __forceinline__ void cp_async8(double* dst_smem, const double* src_gm
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src_gmem), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>   // returns when at most the N most recent groups of this thread are still in flight
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ int wrap_index(int x, int m) {
   x %= m;
@@ -238,6 +241,7 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
         bulk::bulk_g2s(row, srow, (unsigned)p.ws * 8u, &bars[buf]);
         for (int m = 0; m < L; ++m) cp_async8(row - L + m, srow + p.ws - L + m, 8);
       }
+      cp_async_commit();   // one group per unit: the wait below leaves the NEXT unit's group in flight
       return;
     }
     if (p.tiles_per_image > 1 && gridDim.x % p.tiles_per_image != 0) {
@@ -266,6 +270,7 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
         cp_async8(row + (par ? 0 : p.ws - 1), srow + (par ? 0 : p.ws - 1), 8);
         bulk::bulk_g2s(row + par, srow + par, (unsigned)(p.ws - 1) * 8u, &bars[buf]);
       }
+      cp_async_commit();
       return;
     }
     if (threadIdx.x == 0) bulk::mbar_expect_tx(&bars[buf], row_bytes * (unsigned)(nr * ng));
@@ -287,8 +292,9 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
     const int i0 = group > 1 ? 0 : (int)(work - img0 * p.tiles_per_image) * p.tile_h;
     const int th = min(p.tile_h, p.hd - i0);
     __syncthreads();   // the previous unit's readers are done with the other buffer (NBUF 2) / this buffer (NBUF 1) and kflip
+    bool staged_next = false;
     if (NBUF == 2) {
-      if (work + gridDim.x < units) stage(work + gridDim.x, buf ^ 1);
+      if (work + gridDim.x < units) { stage(work + gridDim.x, buf ^ 1); staged_next = true; }
     } else {
       stage(work, 0);
     }
@@ -303,7 +309,9 @@ __global__ void __launch_bounds__(kDirectThreads, 2) direct_bulk_kernel(const __
     }
     bulk::mbar_wait(&bars[buf], buf ? phase1 : phase0);   // (completes at once when the unit has no source rows)
     if (buf) phase1 ^= 1u; else phase0 ^= 1u;
-    if (ODD || p.wrap_h > 0) cp_async_wait_all();                 // this thread's edge / wrapped elements
+    if (ODD || p.wrap_h > 0) {                                     // this thread's edge / wrapped elements of THIS unit
+      if (staged_next) cp_async_wait_group<1>(); else cp_async_wait_group<0>();
+    }
     if (ODD || p.wrap_h > 0 || load_kernel) __syncthreads();      // they, cleared columns and kflip were written by other threads
     const double* S = S0 + buf * bufsz;
     double* d = p.dst + (size_t)img0 * dst_sz;
