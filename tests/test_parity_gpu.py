@@ -575,7 +575,7 @@ def test_strip_mode_shared_kernel_and_rectangles(b2c, oracle, torch_cuda):
 
 
 def test_tuned_square_period_family_vs_oracle(b2c, oracle, torch_cuda):
-    """conv_tuned2.cu: one fused kernel per square period of the menu (16 ... 128).  Each period is hit
+    """conv_tuned2.cu: one fused kernel per square period of the menu (16 ... 160).  Each period is hit
     with several modes / rectangular shapes and checked against the oracle and the any-size kernel."""
     torch = torch_cuda
     rng = np.random.default_rng(41)
@@ -613,7 +613,7 @@ def test_tuned_square_period_family_vs_oracle(b2c, oracle, torch_cuda):
 
 
 def test_tuned_square_period_family_with_per_image_kernels(b2c, oracle, torch_cuda):
-    """Per-image kernels on every square menu period (16 ... 128, 108 included): each image's kernel runs through the
+    """Per-image kernels on every square menu period (16 ... 160, 108 included): each image's kernel runs through the
     forward passes on its own and its spectrum is parked in the CTA's slot (conv_tuned2.cu, PERIMG).  More images
     than resident CTAs would need thousands of them; instead the batch is odd, kernels differ in size up to the
     period itself, and neighbouring images and kernels differ in magnitude by many decades (source and kernel are
