@@ -512,6 +512,12 @@ def run_b2c_arm(args):
              b2c.LINEAR_SAME, 100, 100, 15, 15, 2 * N3, False, SEED3, 10, 8 * (2 * 100 * 100 + 15 * 15)),
             ("configs[4] small-kernel point: 100x100 (*) 3x3 LINEAR_SAME, shared kernel (direct kernel), %d per GPU" % (2 * N3),
              b2c.LINEAR_SAME, 100, 100, 3, 3, 2 * N3, True, SEED3, 20, 8 * (2 * 100 * 100)),
+            ("configs[4] odd-width small-kernel point: 99x99 (*) 3x3 LINEAR_SAME, shared kernel (direct kernel), %d per GPU" % (2 * N3),
+             b2c.LINEAR_SAME, 99, 99, 3, 3, 2 * N3, True, SEED3, 20, 8 * (2 * 99 * 99)),
+            ("configs[4] wrapped small-kernel point: 100x100 (*) 3x3 CIRCULAR_SAME, shared kernel (direct kernel), %d per GPU" % (2 * N3),
+             b2c.CIRCULAR_SAME, 100, 100, 3, 3, 2 * N3, True, SEED3, 20, 8 * (2 * 100 * 100)),
+            ("configs[4] large-kernel point: 100x100 (*) 80x80 LINEAR_FULL, shared kernel (period 200 strip kernel), %d per GPU" % (N3 // 2),
+             b2c.LINEAR_FULL, 100, 100, 80, 80, N3 // 2, True, SEED3, 3, 8 * (100 * 100 + 179 * 179)),
             ("configs[3] short-kernel point: 1x4096 (*) 1x3 LINEAR_SAME rows (direct kernel), %d per GPU" % (4 * N4),
              b2c.LINEAR_SAME, 1, 4096, 1, 3, 4 * N4, True, SEED4, 20, 8 * (4096 + 4096)),
             ("configs[3]: 1x4096 (*) 1x255 LINEAR_SAME rows, shared kernel, %d per GPU" % N4,
